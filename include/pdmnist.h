@@ -1,0 +1,215 @@
+/*
+ * pdmnist.h -- C ABI of libpdmnist_b200.so, the sm_100a native core of
+ * pytorch_distributed_mnist_b200.
+ *
+ * Everything below is `extern "C"`, takes raw device/host pointers and a CUDA
+ * stream, and returns 0 on success or a negative pdm_status.  After a failure
+ * pdm_last_error() (thread-local) describes it.  Python binds these through
+ * ctypes (pytorch_distributed_mnist_b200/ops/_lib.py); nothing here links
+ * against libtorch, so the library also serves C/C++ callers.
+ *
+ * "ref:N" cites /root/reference/multi_proc_single_gpu.py line N: the reference
+ * behaviour each entry point re-implements.  The reference itself ships no
+ * native code; each of these replaces a PyTorch/NCCL/cuBLAS
+ * library call on its path.
+ */
+#ifndef PDMNIST_H_
+#define PDMNIST_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* pdm_stream_t; /* cudaStream_t */
+
+enum pdm_status {
+  PDM_OK = 0,
+  PDM_ERR_ARG = -1,     /* bad argument */
+  PDM_ERR_CUDA = -2,    /* a CUDA runtime call failed */
+  PDM_ERR_STATE = -3,   /* object used before it was set up */
+  PDM_ERR_IO = -4,      /* socket / file error */
+  PDM_ERR_TIMEOUT = -5, /* a peer did not show up in time */
+  PDM_ERR_LIMIT = -6    /* request exceeds a documented maximum */
+};
+
+enum pdm_dtype { PDM_U8 = 0, PDM_F32 = 1, PDM_I64 = 2, PDM_I32 = 3 };
+enum pdm_opt { PDM_OPT_ADAM = 0, PDM_OPT_SGD = 1, PDM_OPT_NONE = 2 };
+
+const char* pdm_last_error(void);
+int pdm_version(void);
+/* 1 when the calling process can see a CUDA device of compute capability 10.x. */
+int pdm_device_ok(int device);
+
+/* ------------------------------------------------------------------------
+ * Geometry of the reference model `Net` = Linear(784, 10)  (ref:119-126).
+ * Flat parameter / optimizer-state buffers are PDM_NET_FLAT floats:
+ *   [0, 7840)     fc.weight, row-major (10, 784)
+ *   [7840, 7850)  fc.bias
+ *   [7850, 7852)  padding (keeps every float4 aligned); never updated
+ * ---------------------------------------------------------------------- */
+#define PDM_NET_IN 784
+#define PDM_NET_OUT 10
+#define PDM_NET_PARAMS 7850
+#define PDM_NET_FLAT 7852
+/* Per-CTA stride of the partial-gradient scratch, in floats. */
+#define PDM_NET_SCRATCH_STRIDE 7856
+#define PDM_NET_MAX_CTAS 148
+/* Floats of scratch pdm_net_train_step needs for a launch of `ctas` CTAs. */
+#define PDM_NET_SCRATCH_FLOATS(ctas) ((size_t)(ctas) * PDM_NET_SCRATCH_STRIDE)
+
+/* Optimizer hyper-parameters, by value per launch.
+ * Adam matches torch.optim.Adam (ref:191): bias-corrected, eps outside the
+ * sqrt, L2 weight decay added to the gradient.  SGD matches torch.optim.SGD
+ * with momentum/dampening 0/nesterov off (the commented-out ref:192-194). */
+typedef struct pdm_hyper {
+  int32_t opt;        /* pdm_opt */
+  float lr;
+  float beta1;        /* Adam beta1, or SGD momentum */
+  float beta2;
+  float eps;
+  float weight_decay;
+  int64_t step;       /* 1-based index of THIS update (Adam bias correction;
+                         SGD uses step==1 to seed the momentum buffer) */
+} pdm_hyper;
+
+/* Peer links for the in-kernel all-reduce (filled by pdm_comm_*; world==1 or
+ * a zeroed struct means single GPU). */
+#define PDM_MAX_RANKS 8
+typedef struct pdm_peers {
+  int32_t world;
+  int32_t rank;
+  uint32_t seq;                      /* flag value of this collective; never 0 */
+  uint32_t pad_;
+  uint64_t* inbox[PDM_MAX_RANKS];    /* inbox[p]: rank p's LL inbox, mapped here */
+  int32_t* status;                   /* device word: nonzero after a peer timeout */
+  uint64_t timeout_ns;               /* 0 = wait forever */
+} pdm_peers;
+
+/* One fused training step of `Net` (ref:83-95 in ONE launch):
+ *   logits = x.W^T + b; loss = cross_entropy(logits, y) (mean over B);
+ *   dW, db; all-reduce over `peers` (sum in rank order, then * 1/world);
+ *   optimizer update of params/m/v in place.
+ *  x        [B,784] device, PDM_U8 (raw MNIST bytes, normalised in-kernel as
+ *           (x/255-0.1307)/0.3081, ref:134) or PDM_F32 (already normalised)
+ *  y        [B] device labels, PDM_U8 / PDM_I64 / PDM_I32
+ *  params,m,v  PDM_NET_FLAT floats each (m,v may be NULL for PDM_OPT_NONE;
+ *           v may be NULL for SGD)
+ *  grad_out optional PDM_NET_FLAT floats: receives the reduced mean gradient
+ *  scratch  PDM_NET_SCRATCH_FLOATS(ctas) floats of device scratch
+ *  sync     2 x uint32 device words, zero-initialised once (grid barrier)
+ *  metrics  optional 4 doubles, device: += {loss*B, correct, B, 0}
+ *  step_out optional 2 floats, device or mapped host: {mean loss, #correct}
+ *  ctas     0 = choose from B; else 1..PDM_NET_MAX_CTAS
+ * The kernel is launched cooperatively; all its CTAs must fit on the GPU. */
+typedef struct pdm_net_step_args {
+  const void* x; int32_t x_dtype;
+  const void* y; int32_t y_dtype;
+  int32_t batch;
+  int32_t ctas;
+  float* params; float* m; float* v;
+  float* grad_out;
+  float* scratch;
+  uint32_t* sync;
+  double* metrics;
+  float* step_out;
+  pdm_hyper hyper;
+  pdm_peers peers;
+} pdm_net_step_args;
+
+int pdm_net_train_step(const pdm_net_step_args* args, pdm_stream_t stream);
+/* CTAs pdm_net_train_step will launch for a batch when args->ctas == 0. */
+int pdm_net_default_ctas(int batch);
+
+/* Forward + loss + top-1 only (ref:106-114).  metrics (4 doubles, device) is
+ * accumulated atomically: += {loss*B, correct, B, 0}.  Any grid size; no scratch. */
+int pdm_net_eval_step(const void* x, int x_dtype, const void* y, int y_dtype, int batch,
+                      const float* params, float* logits_out /* optional [B,10] */,
+                      double* metrics, pdm_stream_t stream);
+
+/* logits[B,10] = x.W^T + b  (Net.forward, ref:126). */
+int pdm_net_forward(const void* x, int x_dtype, int batch, const float* params,
+                    float* logits, pdm_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Flat fused optimizers (one launch for the whole model; replaces the eight
+ * _foreach launches of torch.optim.Adam).
+ * grad may alias a communication bucket.  grad_scale multiplies the gradient
+ * first (1/world for a summed bucket).
+ * ---------------------------------------------------------------------- */
+int pdm_optim_step(float* params, const float* grad, float* m, float* v, size_t n,
+                   const pdm_hyper* hyper, float grad_scale, pdm_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Fused cross-entropy (ref:88): loss, top-1 count and dlogits in one pass.
+ *  logits [B,C] fp32, C <= 32.  dlogits may be NULL (evaluation).
+ * ---------------------------------------------------------------------- */
+int pdm_cross_entropy(const float* logits, const void* y, int y_dtype, int batch, int classes,
+                      float* loss_mean /* device scalar */, float* dlogits, double* metrics,
+                      pdm_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Peer-memory communicator (comm.cu).  Replaces ProcessGroupNCCL + NCCL +
+ * the c10d Reducer on the gradient path (ref:167-168, ref:188-189, ref:91;
+ * SURVEY N2-N4, N7, K9, K14-K16).  One process per GPU; every rank allocates
+ * a symmetric region, exports a 64-byte CUDA IPC handle, and maps all peers.
+ * The handle exchange itself goes through whatever key-value store the caller
+ * has (the tcp:// rendezvous store).  All ranks must issue the same sequence
+ * of collectives.  Offsets are bytes into the region's data area.
+ * ---------------------------------------------------------------------- */
+typedef struct pdm_comm pdm_comm;
+int pdm_comm_create(pdm_comm** out, int rank, int world, int device, size_t data_bytes);
+int pdm_comm_handle(pdm_comm* c, void* out64);                 /* this rank's IPC handle */
+int pdm_comm_connect(pdm_comm* c, const void* handles);        /* world x 64 bytes, rank order */
+void* pdm_comm_data(pdm_comm* c);                              /* local data area (device ptr) */
+size_t pdm_comm_data_bytes(pdm_comm* c);
+int pdm_comm_set_timeout(pdm_comm* c, double seconds);         /* 0 = wait forever; default 30 s */
+int pdm_comm_peers(pdm_comm* c, pdm_peers* out, int advance);  /* links for pdm_net_train_step */
+int pdm_comm_status(pdm_comm* c, int* status);                 /* 0, or 1 + rank that timed out */
+int pdm_comm_barrier(pdm_comm* c, pdm_stream_t stream);
+/* Every rank ends up with root's bytes [offset, offset+bytes) (DDP's initial
+ * parameter broadcast, K15): non-root ranks pull over NVLink. */
+int pdm_comm_broadcast(pdm_comm* c, size_t offset, size_t bytes, int root, pdm_stream_t stream);
+/* Fused all-reduce (rank-ordered sum) * grad_scale + optimizer update.
+ *  algo 0 auto / 1 one-shot (every rank reduces and updates everything) /
+ *       2 two-shot (rank r reduces and updates slice r, then stores the new
+ *         parameters into every replica; m/v of other slices stay stale here)
+ *  hyper->opt == PDM_OPT_NONE: plain all-reduce, result at out_off (must
+ *  differ from grad_off in one-shot mode).
+ *  max_ctas 0 = up to one CTA per SM (the kernel is launched cooperatively). */
+int pdm_comm_allreduce_optim(pdm_comm* c, size_t grad_off, size_t out_off, size_t m_off, size_t v_off,
+                             size_t n_floats, const pdm_hyper* hyper, float grad_scale, int algo,
+                             int max_ctas, pdm_stream_t stream);
+int pdm_comm_destroy(pdm_comm* c);
+
+/* ------------------------------------------------------------------------
+ * Native epoch executor for the fused Net path (engine.cu).  Replaces the
+ * DataLoader worker processes, the per-step pageable H2D copies and the two
+ * per-step host syncs of Trainer.train()/evaluate() (ref:77-116; SURVEY N13,
+ * N14, K1, K2, K12, K13).
+ * ---------------------------------------------------------------------- */
+typedef struct pdm_engine pdm_engine;
+int pdm_engine_create(pdm_engine** out, int device, int max_batch, int slots, int workers);
+int pdm_engine_bind(pdm_engine* e, float* params, float* m, float* v, pdm_comm* comm /* may be NULL */);
+/* Host-resident dataset: images [n,784] uint8, labels [n] uint8.  Not copied; must outlive the runs. */
+int pdm_engine_set_dataset(pdm_engine* e, const uint8_t* images, const uint8_t* labels, int64_t n);
+/* ceil(count/batch) steps in `indices` order.  train: hyper->step = index of the first update;
+ * step_results (host, [nsteps][2]) gets {mean loss, correct} per step.  Blocks until done. */
+int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int batch, int train,
+                   const pdm_hyper* hyper, int ctas, float* step_results, float* device_ms);
+/* nsteps training steps over a device-resident pool of samples; no host traffic. */
+int pdm_engine_run_device(pdm_engine* e, const uint8_t* dev_images, const uint8_t* dev_labels,
+                          int64_t pool_samples, int batch, int64_t nsteps, const pdm_hyper* hyper,
+                          int ctas, float* device_ms);
+int pdm_engine_metrics(pdm_engine* e, double out[4], int reset);
+void* pdm_engine_scratch(pdm_engine* e);
+void* pdm_engine_sync_words(pdm_engine* e);
+void* pdm_engine_metrics_ptr(pdm_engine* e);
+int pdm_engine_destroy(pdm_engine* e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PDMNIST_H_ */

@@ -1,0 +1,590 @@
+// net_step.cu -- the reference model's whole training step as ONE sm_100a kernel.
+//
+// Reference path being replaced (ref:N = /root/reference/multi_proc_single_gpu.py):
+//   ref:87  model(data)            -> cuBLAS addmm            
+//   ref:88  F.cross_entropy        -> ATen softmax + nll      (K4)
+//   ref:91  loss.backward()        -> nll/softmax bwd, cuBLAS mm, column sum (K5-K7)
+//           DDP reducer            -> 4 bucket copies + ncclAllReduce      (K8-K10)
+//   ref:92  optimizer.step()       -> 8 _foreach launches                  (K11)
+//   ref:94-95 loss.item(), argmax/eq/sum/.item() -> 4 kernels + 2 host syncs (K12-K13)
+// ~25 launches and two syncs for 16 MFLOP.  Here: one cooperative launch.
+//
+// Shape of the kernel (B = local batch, G = CTAs, RT = rows per tile):
+//   phase 1  CTA c owns a contiguous slice of the batch.  Thread t < 196 owns
+//            four input columns [4t, 4t+4): it keeps W[:, 4t..4t+3] (40 regs)
+//            and its partial dW (40 regs) in registers for the whole kernel and
+//            streams the rows through (raw uint8 -> LUT-normalised fp32, or
+//            fp32).  Per tile: partial logits are transpose-reduced with warp
+//            shuffles (~N shuffles for N values instead of 5N), finished
+//            through smem, soft-maxed by 16-lane groups (loss, top-1, dlogits),
+//            then dW += dlogits^T x from the same registers.  x is read once.
+//   grid barrier
+//   phase 2  The 1963 float4 of the flat gradient are spread over all CTAs.
+//            Each thread sums the G partials in CTA order (deterministic),
+//            exchanges with the peers (LL protocol: 8-byte {value, flag}
+//            units pushed straight into every peer's inbox over NVLink,
+//            receiver polls its own memory), sums in rank order so every rank
+//            gets bit-identical parameters, scales by 1/world and applies
+//            Adam / SGD-momentum in registers.
+// Metrics never leave the device unless asked: {loss*B, correct, B} are
+// accumulated into a device buffer, and optionally {mean loss, correct} of
+// this step is written to step_out (which may be mapped host memory).
+//
+// tcgen05 note: with N = 10 the forward/wgrad GEMMs are
+// 2 MFLOP at B = 64; a UMMA tile would be 94% padding and the step is bound
+// by launch + two memory round trips, not math.  The FMA form above is the
+// measured-fastest form for this model; the tcgen05/TMA machinery lives in
+// gemm_tcgen05.cu and serves the CNN's GEMM-shaped layers.
+#include "common.cuh"
+
+#include <math.h>
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kIn = PDM_NET_IN;          // 784
+constexpr int kOut = PDM_NET_OUT;        // 10
+constexpr int kCols4 = kIn / 4;          // 196 float4 columns
+constexpr int kFlat4 = PDM_NET_FLAT / 4; // 1963 float4 in the flat parameter vector
+constexpr int kStride = PDM_NET_SCRATCH_STRIDE;
+constexpr int kFwdWarps = 7;             // warps that own columns (7*32 = 224 >= 196)
+constexpr float kMean = 0.1307f;
+constexpr float kStd = 0.3081f;
+
+struct OptConsts {
+  int opt;
+  int first;        // SGD: step == 1 seeds the momentum buffer
+  float lr, beta1, beta2, eps, wd;
+  float step_size;  // Adam: lr / (1 - beta1^t)
+  float bc2_sqrt;   // Adam: sqrt(1 - beta2^t)
+  float inv_world;
+};
+
+struct KernelArgs {
+  const void* x;
+  const void* y;
+  int y_dtype;
+  int batch;
+  int rows_per_cta;
+  float inv_batch;
+  float* params;
+  float* m;
+  float* v;
+  float* grad_out;
+  float* scratch;
+  uint32_t* sync;
+  double* metrics;
+  float* step_out;
+  float* logits_out;
+  OptConsts oc;
+  pdm_peers peers;
+};
+
+__device__ __forceinline__ int load_label(const void* y, int dtype, int row) {
+  int v;
+  if (dtype == PDM_U8) v = ((const uint8_t*)y)[row];
+  else if (dtype == PDM_I64) v = (int)((const long long*)y)[row];
+  else v = ((const int*)y)[row];
+  return min(max(v, 0), kOut - 1);
+}
+
+// Reduce N per-lane values across the 32 lanes of a warp with N-ish shuffles.
+// On return lane L holds in v[i] (i < N/32) the warp total of value L*(N/32)+i.
+template <int N>
+__device__ __forceinline__ void warp_transpose_reduce(float (&v)[N], int lane) {
+  static_assert(N % 32 == 0, "N must be a multiple of 32");
+#pragma unroll
+  for (int off = 16, h = N / 2; off >= 1; off >>= 1, h >>= 1) {
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < h; ++i) {
+      const float keep = upper ? v[i + h] : v[i];
+      const float send = upper ? v[i] : v[i + h];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+}
+
+template <typename XT> struct RawRow;
+template <> struct RawRow<uint8_t> {
+  using type = uint32_t;
+  static __device__ __forceinline__ type load(const void* x, int row, int t) {
+    return __ldg(reinterpret_cast<const uint32_t*>(static_cast<const uint8_t*>(x) + (size_t)row * kIn) + t);
+  }
+  static __device__ __forceinline__ void decode(type raw, const float* lut, float (&o)[4]) {
+    o[0] = lut[raw & 255u];
+    o[1] = lut[(raw >> 8) & 255u];
+    o[2] = lut[(raw >> 16) & 255u];
+    o[3] = lut[raw >> 24];
+  }
+};
+template <> struct RawRow<float> {
+  using type = float4;
+  static __device__ __forceinline__ type load(const void* x, int row, int t) {
+    return __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(x) + (size_t)row * kIn) + t);
+  }
+  static __device__ __forceinline__ void decode(type raw, const float*, float (&o)[4]) {
+    o[0] = raw.x; o[1] = raw.y; o[2] = raw.z; o[3] = raw.w;
+  }
+};
+
+template <int RT>
+struct Smem {
+  static constexpr int kVals = RT * kOut;                 // logits per tile
+  static constexpr int kPad = ((kVals + 31) / 32) * 32;   // padded for the transpose-reduce
+  float lut[256];
+  float red[kFwdWarps][kPad];
+  float dl[RT][12];
+  int ys[RT];
+  float bias[12];
+  float wloss[8];
+  float wcorrect[8];
+};
+
+// Apply one optimizer update to a float4 lane group.
+__device__ __forceinline__ void opt_update(const OptConsts& oc, float g, float& p, float& m, float& v) {
+  if (oc.opt == PDM_OPT_ADAM) {
+    if (oc.wd != 0.f) g = fmaf(oc.wd, p, g);
+    m = m + (1.f - oc.beta1) * (g - m);                  // exp_avg.lerp_(grad, 1-beta1)
+    v = v * oc.beta2 + (1.f - oc.beta2) * g * g;         // mul_(beta2).addcmul_(g, g, 1-beta2)
+    const float denom = sqrtf(v) / oc.bc2_sqrt + oc.eps;
+    p = p - oc.step_size * (m / denom);                  // addcdiv_(exp_avg, denom, -step_size)
+  } else if (oc.opt == PDM_OPT_SGD) {
+    if (oc.wd != 0.f) g = fmaf(oc.wd, p, g);
+    if (oc.beta1 != 0.f) {
+      m = oc.first ? g : (m * oc.beta1 + g);
+      g = m;
+    }
+    p = p - oc.lr * g;
+  }
+}
+
+// MODE 0: train (phase 1 + barrier + phase 2).  MODE 1: eval/forward only.
+template <int RT, typename XT, int MODE>
+__global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant__ KernelArgs a) {
+  using Raw = RawRow<XT>;
+  using SM = Smem<RT>;
+  __shared__ SM sm;
+
+  const int tid = threadIdx.x;
+  const int lane = tid & 31;
+  const int warp = tid >> 5;
+  const int cta = blockIdx.x;
+  const int G = gridDim.x;
+  const bool owns_cols = tid < kCols4;
+
+  // ---- one-time per CTA: LUT, bias, this thread's weight columns ----------
+  if (sizeof(XT) == 1) {
+    // Bit-exact torchvision ToTensor (/255) + Normalize ((x-mean)/std), ref:132-135.
+    sm.lut[tid] = __fdiv_rn(__fdiv_rn((float)tid, 255.0f) - kMean, kStd);
+  }
+  if (tid < 12) sm.bias[tid] = tid < kOut ? a.params[kIn * kOut + tid] : 0.f;
+
+  float w[kOut][4];
+  float g[kOut][4];
+#pragma unroll
+  for (int c = 0; c < kOut; ++c) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { w[c][i] = 0.f; g[c][i] = 0.f; }
+  }
+  if (owns_cols) {
+#pragma unroll
+    for (int c = 0; c < kOut; ++c) {
+      const float4 t4 = *reinterpret_cast<const float4*>(a.params + c * kIn + 4 * tid);
+      w[c][0] = t4.x; w[c][1] = t4.y; w[c][2] = t4.z; w[c][3] = t4.w;
+    }
+  }
+  float db = 0.f;          // threads 196..205: bias gradient of class tid-196
+  float my_loss = 0.f;     // softmax threads with c == 0
+  float my_correct = 0.f;
+
+  const int row_begin = cta * a.rows_per_cta;
+  const int row_end = min(a.batch, row_begin + a.rows_per_cta);
+
+  typename Raw::type raw[RT];
+#pragma unroll
+  for (int r = 0; r < RT; ++r) {
+    raw[r] = typename Raw::type();
+    if (owns_cols && row_begin + r < row_end) raw[r] = Raw::load(a.x, row_begin + r, tid);
+  }
+  __syncthreads();
+
+  for (int row0 = row_begin; row0 < row_end; row0 += RT) {
+    const int nrows = min(RT, row_end - row0);
+    if (a.y != nullptr && tid < RT) sm.ys[tid] = tid < nrows ? load_label(a.y, a.y_dtype, row0 + tid) : 0;
+
+    // decode this tile, prefetch the next one
+    float xr[RT][4];
+#pragma unroll
+    for (int r = 0; r < RT; ++r) Raw::decode(raw[r], sm.lut, xr[r]);
+#pragma unroll
+    for (int r = 0; r < RT; ++r) {
+      const int nr = row0 + RT + r;
+      if (owns_cols && nr < row_end) raw[r] = Raw::load(a.x, nr, tid);
+    }
+
+    // ---- forward partials: v[r*10+c] = sum_i x[r][i] * W[c][i] ------------
+    if (warp < kFwdWarps) {
+      float v[SM::kPad];
+#pragma unroll
+      for (int r = 0; r < RT; ++r) {
+#pragma unroll
+        for (int c = 0; c < kOut; ++c) {
+          float s = xr[r][0] * w[c][0];
+          s = fmaf(xr[r][1], w[c][1], s);
+          s = fmaf(xr[r][2], w[c][2], s);
+          s = fmaf(xr[r][3], w[c][3], s);
+          v[r * kOut + c] = owns_cols ? s : 0.f;
+        }
+      }
+#pragma unroll
+      for (int i = SM::kVals; i < SM::kPad; ++i) v[i] = 0.f;
+      warp_transpose_reduce<SM::kPad>(v, lane);
+      constexpr int per = SM::kPad / 32;
+#pragma unroll
+      for (int i = 0; i < per; ++i) sm.red[warp][lane * per + i] = v[i];
+    }
+    __syncthreads();
+
+    // ---- softmax / loss / top-1 / dlogits: 16-lane group per row ----------
+    if (tid < RT * 16) {
+      const int r = tid >> 4;
+      const int c = tid & 15;
+      const bool live = c < kOut;
+      float z = -INFINITY;
+      if (live) {
+        z = sm.bias[c];
+#pragma unroll
+        for (int wv = 0; wv < kFwdWarps; ++wv) z += sm.red[wv][r * kOut + c];
+        if (a.logits_out != nullptr && r < nrows) a.logits_out[(size_t)(row0 + r) * kOut + c] = z;
+      }
+      if (a.y != nullptr) {
+        float mx = z;
+#pragma unroll
+        for (int off = 8; off >= 1; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+        const float e = live ? expf(z - mx) : 0.f;
+        float s = e;
+#pragma unroll
+        for (int off = 8; off >= 1; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+        const int y = sm.ys[r];
+        const float zy = __shfl_sync(0xffffffffu, z, (lane & 16) + y);
+        const bool beats = live && (z > zy || (z == zy && c < y));
+        const uint32_t ballot = __ballot_sync(0xffffffffu, beats);
+        const bool hit = ((ballot >> (lane & 16)) & 0xffffu) == 0u;
+        const bool valid = r < nrows;
+        if (MODE == 0) {
+          float d = 0.f;
+          if (valid && live) d = (e / s - (c == y ? 1.f : 0.f)) * a.inv_batch;
+          if (c < 12) sm.dl[r][c] = d;
+        }
+        if (c == 0 && valid) {
+          my_loss += (mx + logf(s)) - zy;
+          my_correct += hit ? 1.f : 0.f;
+        }
+      }
+    }
+    if (MODE == 0) {
+      __syncthreads();
+      // ---- backward: dW[:, cols] += dlogits^T x, db += colsum(dlogits) -----
+      if (owns_cols) {
+#pragma unroll
+        for (int r = 0; r < RT; ++r) {
+          const float4 d0 = *reinterpret_cast<const float4*>(&sm.dl[r][0]);
+          const float4 d1 = *reinterpret_cast<const float4*>(&sm.dl[r][4]);
+          const float4 d2 = *reinterpret_cast<const float4*>(&sm.dl[r][8]);
+          const float d[kOut] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w, d2.x, d2.y};
+#pragma unroll
+          for (int c = 0; c < kOut; ++c) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) g[c][i] = fmaf(d[c], xr[r][i], g[c][i]);
+          }
+        }
+      } else if (tid < kCols4 + kOut) {
+#pragma unroll
+        for (int r = 0; r < RT; ++r) db += sm.dl[r][tid - kCols4];
+      }
+    } else {
+      __syncthreads();  // red/ys are rewritten by the next tile
+    }
+  }
+
+  // ---- CTA totals of loss / correct ----------------------------------------
+  if (a.y != nullptr) {
+    // only lanes 0 and 16 of warps < RT*16/32 carry values
+    float l = my_loss + __shfl_xor_sync(0xffffffffu, my_loss, 16);
+    float k = my_correct + __shfl_xor_sync(0xffffffffu, my_correct, 16);
+    if (lane == 0) { sm.wloss[warp] = l; sm.wcorrect[warp] = k; }
+  }
+  __syncthreads();
+
+  if (MODE == 1) {
+    if (a.y != nullptr && tid == 0) {
+      float l = 0.f, k = 0.f;
+      constexpr int nw = (RT * 16 + 31) / 32;
+#pragma unroll
+      for (int i = 0; i < nw; ++i) { l += sm.wloss[i]; k += sm.wcorrect[i]; }
+      const int rows = max(0, row_end - row_begin);
+      if (a.metrics != nullptr && rows > 0) {
+        atomicAdd(a.metrics + 0, (double)l);
+        atomicAdd(a.metrics + 1, (double)k);
+        atomicAdd(a.metrics + 2, (double)rows);
+      }
+    }
+    return;
+  }
+
+  // ---- publish this CTA's partial gradient ---------------------------------
+  float* mine = a.scratch + (size_t)cta * kStride;
+  if (owns_cols) {
+#pragma unroll
+    for (int c = 0; c < kOut; ++c)
+      __stcg(reinterpret_cast<float4*>(mine + c * kIn + 4 * tid), make_float4(g[c][0], g[c][1], g[c][2], g[c][3]));
+  } else if (tid < kCols4 + kOut) {
+    __stcg(mine + kIn * kOut + (tid - kCols4), db);
+  } else if (tid == kCols4 + kOut) {
+    float l = 0.f, k = 0.f;
+    constexpr int nw = (RT * 16 + 31) / 32;
+#pragma unroll
+    for (int i = 0; i < nw; ++i) { l += sm.wloss[i]; k += sm.wcorrect[i]; }
+    __stcg(mine + PDM_NET_PARAMS, l);
+    __stcg(mine + PDM_NET_PARAMS + 1, k);
+  }
+
+  if (G > 1) grid_barrier(a.sync, (uint32_t)G);
+  else __syncthreads();
+
+  // ---- phase 2: reduce partials, all-reduce with peers, optimizer ----------
+  const int per_cta = (kFlat4 + G - 1) / G;
+  const int j_end = min(kFlat4, (cta + 1) * per_cta);
+  const int W = a.peers.world > 1 ? a.peers.world : 1;
+  const uint32_t seq = a.peers.seq;
+  for (int j = cta * per_cta + tid; j < j_end; j += kThreads) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float* src = a.scratch + 4 * j;
+#pragma unroll 8
+    for (int c = 0; c < G; ++c) {
+      const float4 t4 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)c * kStride));
+      acc.x += t4.x; acc.y += t4.y; acc.z += t4.z; acc.w += t4.w;
+    }
+    if (j == kFlat4 - 1) {
+      // lanes z, w of the last float4 are this rank's {sum of losses, correct}
+      if (a.step_out != nullptr) {
+        a.step_out[0] = acc.z * a.inv_batch;
+        a.step_out[1] = acc.w;
+      }
+      if (a.metrics != nullptr) {
+        a.metrics[0] += (double)acc.z;
+        a.metrics[1] += (double)acc.w;
+        a.metrics[2] += (double)a.batch;
+      }
+      acc.z = 0.f;
+      acc.w = 0.f;
+    }
+
+    if (W > 1) {
+      const size_t par = (size_t)(seq & 1u) * W;
+      const size_t slot = ((par + a.peers.rank) * kFlat4 + j) * 4;
+      for (int p = 0; p < W; ++p) {
+        if (p == a.peers.rank) continue;
+        uint64_t* dst = a.peers.inbox[p] + slot;
+        ll_store2(dst, acc.x, acc.y, seq);
+        ll_store2(dst + 2, acc.z, acc.w, seq);
+      }
+      float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+      const uint64_t* inbox = a.peers.inbox[a.peers.rank];
+      uint64_t t0 = 0;
+      for (int p = 0; p < W; ++p) {
+        float4 q = acc;
+        if (p != a.peers.rank) {
+          const uint64_t* s = inbox + ((par + p) * kFlat4 + j) * 4;
+          uint32_t spins = 0;
+          bool ok0 = false, ok1 = false;
+          while (true) {
+            if (!ok0) ok0 = ll_load2(s, seq, q.x, q.y);
+            if (!ok1) ok1 = ll_load2(s + 2, seq, q.z, q.w);
+            if (ok0 && ok1) break;
+            if ((++spins & 1023u) == 0u && a.peers.timeout_ns != 0) {
+              const uint64_t now = globaltimer_ns();
+              if (t0 == 0) t0 = now;
+              else if (now - t0 > a.peers.timeout_ns) {
+                if (a.peers.status != nullptr) atomicExch(a.peers.status, 1 + p);
+                break;
+              }
+            }
+          }
+        }
+        sum.x += q.x; sum.y += q.y; sum.z += q.z; sum.w += q.w;
+      }
+      acc = sum;
+    }
+    const float iw = a.oc.inv_world;
+    acc.x *= iw; acc.y *= iw; acc.z *= iw; acc.w *= iw;
+    if (a.grad_out != nullptr) *reinterpret_cast<float4*>(a.grad_out + 4 * j) = acc;
+
+    if (a.oc.opt != PDM_OPT_NONE) {
+      float4 p4 = *reinterpret_cast<float4*>(a.params + 4 * j);
+      float4 m4 = make_float4(0.f, 0.f, 0.f, 0.f), v4 = m4;
+      if (a.m != nullptr) m4 = *reinterpret_cast<float4*>(a.m + 4 * j);
+      if (a.v != nullptr) v4 = *reinterpret_cast<float4*>(a.v + 4 * j);
+      opt_update(a.oc, acc.x, p4.x, m4.x, v4.x);
+      opt_update(a.oc, acc.y, p4.y, m4.y, v4.y);
+      if (j != kFlat4 - 1) {  // the last two floats are padding, not parameters
+        opt_update(a.oc, acc.z, p4.z, m4.z, v4.z);
+        opt_update(a.oc, acc.w, p4.w, m4.w, v4.w);
+      }
+      *reinterpret_cast<float4*>(a.params + 4 * j) = p4;
+      if (a.m != nullptr) *reinterpret_cast<float4*>(a.m + 4 * j) = m4;
+      if (a.v != nullptr) *reinterpret_cast<float4*>(a.v + 4 * j) = v4;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+constexpr int kRT = 8;
+
+OptConsts make_consts(const pdm_hyper& h, int world) {
+  OptConsts oc;
+  memset(&oc, 0, sizeof(oc));
+  oc.opt = h.opt;
+  oc.first = h.step <= 1;
+  oc.lr = h.lr;
+  oc.beta1 = h.beta1;
+  oc.beta2 = h.beta2;
+  oc.eps = h.eps;
+  oc.wd = h.weight_decay;
+  if (h.opt == PDM_OPT_ADAM) {
+    const double step = (double)(h.step < 1 ? 1 : h.step);
+    const double bc1 = 1.0 - pow((double)h.beta1, step);
+    const double bc2 = 1.0 - pow((double)h.beta2, step);
+    oc.step_size = (float)((double)h.lr / bc1);
+    oc.bc2_sqrt = (float)sqrt(bc2);
+  }
+  oc.inv_world = world > 1 ? 1.0f / (float)world : 1.0f;
+  return oc;
+}
+
+void plan_rows(int batch, int want_ctas, int* ctas, int* rows_per_cta) {
+  int g = want_ctas > 0 ? want_ctas : (batch + kRT - 1) / kRT;
+  if (g > PDM_NET_MAX_CTAS) g = PDM_NET_MAX_CTAS;
+  if (g < 1) g = 1;
+  int rpc = (batch + g - 1) / g;
+  if (rpc < 1) rpc = 1;
+  g = (batch + rpc - 1) / rpc;
+  if (g < 1) g = 1;
+  *ctas = g;
+  *rows_per_cta = rpc;
+}
+
+template <int MODE>
+cudaError_t launch(const KernelArgs& ka, int x_dtype, int ctas, cudaStream_t stream) {
+  KernelArgs local = ka;
+  void* params[] = {&local};
+  const void* fn = x_dtype == PDM_U8 ? (const void*)net_kernel<kRT, uint8_t, MODE>
+                                     : (const void*)net_kernel<kRT, float, MODE>;
+  if (MODE == 0 && ctas > 1)
+    return cudaLaunchCooperativeKernel(fn, dim3(ctas), dim3(kThreads), params, 0, stream);
+  return cudaLaunchKernel(fn, dim3(ctas), dim3(kThreads), params, 0, stream);
+}
+
+}  // namespace
+
+extern "C" int pdm_net_default_ctas(int batch) {
+  int g, rpc;
+  plan_rows(batch, 0, &g, &rpc);
+  return g;
+}
+
+extern "C" int pdm_net_train_step(const pdm_net_step_args* args, pdm_stream_t stream) {
+  PDM_REQUIRE(args != nullptr, PDM_ERR_ARG, "pdm_net_train_step: args is NULL");
+  PDM_REQUIRE(args->batch >= 1, PDM_ERR_ARG, "pdm_net_train_step: batch must be >= 1 (got %d)", args->batch);
+  PDM_REQUIRE(args->x && args->y && args->params && args->scratch && args->sync, PDM_ERR_ARG,
+              "pdm_net_train_step: x, y, params, scratch and sync are required");
+  PDM_REQUIRE(args->x_dtype == PDM_U8 || args->x_dtype == PDM_F32, PDM_ERR_ARG,
+              "pdm_net_train_step: x_dtype must be PDM_U8 or PDM_F32");
+  PDM_REQUIRE(args->y_dtype == PDM_U8 || args->y_dtype == PDM_I64 || args->y_dtype == PDM_I32, PDM_ERR_ARG,
+              "pdm_net_train_step: y_dtype must be PDM_U8, PDM_I64 or PDM_I32");
+  PDM_REQUIRE(args->ctas >= 0 && args->ctas <= PDM_NET_MAX_CTAS, PDM_ERR_LIMIT,
+              "pdm_net_train_step: ctas %d outside [0, %d]", args->ctas, PDM_NET_MAX_CTAS);
+  const pdm_hyper& h = args->hyper;
+  PDM_REQUIRE(h.opt == PDM_OPT_ADAM || h.opt == PDM_OPT_SGD || h.opt == PDM_OPT_NONE, PDM_ERR_ARG,
+              "pdm_net_train_step: unknown optimizer %d", h.opt);
+  PDM_REQUIRE(h.opt != PDM_OPT_ADAM || (args->m && args->v), PDM_ERR_ARG,
+              "pdm_net_train_step: Adam needs m and v");
+  PDM_REQUIRE(!(h.opt == PDM_OPT_SGD && h.beta1 != 0.f) || args->m, PDM_ERR_ARG,
+              "pdm_net_train_step: SGD with momentum needs m");
+  const int world = args->peers.world > 1 ? args->peers.world : 1;
+  PDM_REQUIRE(world <= PDM_MAX_RANKS, PDM_ERR_LIMIT, "pdm_net_train_step: world %d > %d", world, PDM_MAX_RANKS);
+  if (world > 1) {
+    PDM_REQUIRE(args->peers.seq != 0, PDM_ERR_ARG, "pdm_net_train_step: peers.seq must be non-zero");
+    PDM_REQUIRE(args->peers.rank >= 0 && args->peers.rank < world, PDM_ERR_ARG, "pdm_net_train_step: bad rank");
+    for (int p = 0; p < world; ++p)
+      PDM_REQUIRE(args->peers.inbox[p] != nullptr, PDM_ERR_STATE, "pdm_net_train_step: inbox[%d] not mapped", p);
+  }
+
+  KernelArgs ka;
+  memset(&ka, 0, sizeof(ka));
+  int ctas = 0;
+  plan_rows(args->batch, args->ctas, &ctas, &ka.rows_per_cta);
+  ka.x = args->x;
+  ka.y = args->y;
+  ka.y_dtype = args->y_dtype;
+  ka.batch = args->batch;
+  ka.inv_batch = 1.0f / (float)args->batch;
+  ka.params = args->params;
+  ka.m = args->m;
+  ka.v = args->v;
+  ka.grad_out = args->grad_out;
+  ka.scratch = args->scratch;
+  ka.sync = args->sync;
+  ka.metrics = args->metrics;
+  ka.step_out = args->step_out;
+  ka.oc = make_consts(h, world);
+  ka.peers = args->peers;
+  ka.peers.world = world;
+  PDM_CHECK_CUDA(launch<0>(ka, args->x_dtype, ctas, (cudaStream_t)stream));
+  return PDM_OK;
+}
+
+static int eval_like(const void* x, int x_dtype, const void* y, int y_dtype, int batch, const float* params,
+                     float* logits_out, double* metrics, cudaStream_t stream, const char* who) {
+  PDM_REQUIRE(batch >= 1, PDM_ERR_ARG, "%s: batch must be >= 1 (got %d)", who, batch);
+  PDM_REQUIRE(x && params, PDM_ERR_ARG, "%s: x and params are required", who);
+  PDM_REQUIRE(x_dtype == PDM_U8 || x_dtype == PDM_F32, PDM_ERR_ARG, "%s: x_dtype must be PDM_U8 or PDM_F32", who);
+  KernelArgs ka;
+  memset(&ka, 0, sizeof(ka));
+  ka.x = x;
+  ka.y = y;
+  ka.y_dtype = y_dtype;
+  ka.batch = batch;
+  ka.rows_per_cta = kRT;
+  int ctas = (batch + kRT - 1) / kRT;
+  const int cap = PDM_NET_MAX_CTAS * 8;  // a few waves at most; then each CTA loops
+  if (ctas > cap) {
+    ka.rows_per_cta = ((batch + cap - 1) / cap + kRT - 1) / kRT * kRT;
+    ctas = (batch + ka.rows_per_cta - 1) / ka.rows_per_cta;
+  }
+  ka.inv_batch = 1.0f / (float)batch;
+  ka.params = const_cast<float*>(params);
+  ka.metrics = metrics;
+  ka.logits_out = logits_out;
+  ka.oc.opt = PDM_OPT_NONE;
+  PDM_CHECK_CUDA(launch<1>(ka, x_dtype, ctas, stream));
+  return PDM_OK;
+}
+
+extern "C" int pdm_net_eval_step(const void* x, int x_dtype, const void* y, int y_dtype, int batch,
+                                 const float* params, float* logits_out, double* metrics,
+                                 pdm_stream_t stream) {
+  PDM_REQUIRE(y != nullptr, PDM_ERR_ARG, "pdm_net_eval_step: y is required");
+  return eval_like(x, x_dtype, y, y_dtype, batch, params, logits_out, metrics, (cudaStream_t)stream,
+                   "pdm_net_eval_step");
+}
+
+extern "C" int pdm_net_forward(const void* x, int x_dtype, int batch, const float* params, float* logits,
+                               pdm_stream_t stream) {
+  PDM_REQUIRE(logits != nullptr, PDM_ERR_ARG, "pdm_net_forward: logits is required");
+  return eval_like(x, x_dtype, nullptr, PDM_U8, batch, params, logits, nullptr, (cudaStream_t)stream,
+                   "pdm_net_forward");
+}

@@ -1,0 +1,139 @@
+"""``Trainer`` -- same constructor and return values as the reference's
+(ref:68-116): ``train()`` runs one epoch and returns ``(Average, Accuracy)``;
+``evaluate()`` does the same over the test loader under ``no_grad``.
+
+Two execution paths behind that surface:
+
+* **fused** (CUDA + ``Net`` + our optimizer + our loader): the whole epoch is
+  handed to the native engine -- C++ loader threads, one packed H2D copy, one
+  fused kernel and one 8-byte readback per step, nothing synchronous
+  (``ops.engine``).  The per-step {loss, correct} pairs come back after the
+  last step and are folded exactly the way the reference folds
+  ``loss.item()`` / ``Accuracy.update`` (ref:94-95), so the printed numbers
+  mean the same thing.
+* **generic** (CPU/gloo, the CNN, user models): the reference's loop shape
+  (ref:83-95) with device-side metric accumulation instead of two
+  ``.item()`` syncs per step; on CUDA the loss is the fused cross-entropy op.
+"""
+from __future__ import annotations
+
+import torch
+
+from .data.loader import MNISTDataLoader
+from .metrics import Accuracy, Average, DeviceMetrics
+from .models.net import Net
+from .ops import _lib
+from .ops.loss import cross_entropy
+from .optim import _FusedBase
+
+
+def _unwrap(model):
+    return model.module if hasattr(model, 'module') and isinstance(model.module, torch.nn.Module) else model
+
+
+class Trainer(object):
+
+    def __init__(self, model, optimizer, train_loader, test_loader, device, fused='auto', ctas=0,
+                 loader_workers=None):
+        self.model = model
+        self.optimizer = optimizer
+        self.train_loader = train_loader
+        self.test_loader = test_loader
+        self.device = torch.device(device)
+        self.ctas = ctas
+        self.engine = None
+        self.last_train_ms = None      # device time of the last fused epoch
+        self._metrics = None
+        want = fused in ('auto', True, 'on')
+        if want and self._fused_eligible():
+            from .ops.engine import NetEngine
+            workers = loader_workers if loader_workers is not None else max(1, getattr(train_loader, 'num_workers', 1))
+            max_batch = max(train_loader.batch_size, test_loader.batch_size if test_loader is not None else 1)
+            comm = getattr(model, 'comm', None) if getattr(model, 'uses_peer', False) else None
+            self.engine = NetEngine(self.optimizer.flat, self.optimizer, comm=comm, device=self.device,
+                                    max_batch=max_batch, slots=8, workers=workers)
+        elif fused in (True, 'on'):
+            raise RuntimeError('fused path requested but not available: needs a CUDA device, the native library, '
+                               'the reference Net, a Fused optimizer and MNISTDataLoader inputs')
+
+    def _fused_eligible(self):
+        if self.device.type != 'cuda' or not torch.cuda.is_available():
+            return False
+        if not isinstance(_unwrap(self.model), Net) or not isinstance(self.optimizer, _FusedBase):
+            return False
+        if not isinstance(self.train_loader, MNISTDataLoader):
+            return False
+        if self.test_loader is not None and not isinstance(self.test_loader, MNISTDataLoader):
+            return False
+        if self.optimizer.flat.numel != _lib.NET_FLAT or not self.optimizer.flat.params.is_cuda:
+            return False
+        world = getattr(self.model, 'world', 1)
+        if world > 1 and not getattr(self.model, 'uses_peer', False):
+            return False       # stock-collective fallback: gradients go through torch.distributed
+        _lib.lib()             # on a GPU box a missing native library is an error, not a fallback
+        return True
+
+    # ------------------------------------------------------------------ train
+    def train(self):
+        self.model.train()
+        train_loss = Average()
+        train_acc = Accuracy()
+        if self.engine is not None:
+            loader = self.train_loader
+            self.engine.set_dataset(loader.images, loader.labels)
+            idx = loader.epoch_indices()
+            steps, ms = self.engine.train(idx, loader.batch_size, ctas=self.ctas)
+            self.last_train_ms = ms
+            self.engine.metrics(reset=True)
+            n = idx.numel()
+            for i in range(steps.shape[0]):
+                b = min(loader.batch_size, n - i * loader.batch_size)
+                train_loss.update(float(steps[i, 0]), b)
+                train_acc.update_counts(int(round(float(steps[i, 1]))), b)
+            return train_loss, train_acc
+
+        dm = self._device_metrics()
+        for data, target in self.train_loader:
+            data = data.to(self.device, non_blocking=True)
+            target = target.to(self.device, non_blocking=True)
+            output = self.model(data)
+            self.optimizer.zero_grad()
+            loss = cross_entropy(output, target, dm.buf)
+            loss.backward()
+            self.optimizer.step()
+        return dm.drain(train_loss, train_acc)
+
+    # --------------------------------------------------------------- evaluate
+    @torch.no_grad()
+    def evaluate(self):
+        self.model.eval()
+        test_loss = Average()
+        test_acc = Accuracy()
+        if self.engine is not None:
+            loader = self.test_loader
+            self.engine.set_dataset(loader.images, loader.labels)
+            self.engine.metrics(reset=True)
+            self.engine.evaluate(loader.epoch_indices(), loader.batch_size)
+            loss_sum, correct, samples = self.engine.metrics(reset=True)
+            test_loss.update_sum(loss_sum, samples)
+            test_acc.update_counts(correct, samples)
+            return test_loss, test_acc
+
+        dm = self._device_metrics()
+        for data, target in self.test_loader:
+            data = data.to(self.device, non_blocking=True)
+            target = target.to(self.device, non_blocking=True)
+            output = self.model(data)
+            cross_entropy(output, target, dm.buf)
+        return dm.drain(test_loss, test_acc)
+
+    def _device_metrics(self):
+        if self._metrics is None:
+            self._metrics = DeviceMetrics(self.device)
+        self._metrics.zero_()
+        return self._metrics
+
+    def close(self):
+        if self.engine is not None:
+            self.engine.close()
+            self.engine = None
