@@ -7,6 +7,8 @@
   launcher's ``MASTER_ADDR/MASTER_PORT`` are ignored; rendezvous uses
   ``--init-method``.
 """
+import os
+
 import torch.multiprocessing as mp
 
 
@@ -26,6 +28,12 @@ def run_spawn(proc_id, args):
 def run_dist_launch(args):
     # single node, multiple GPUs: with torch.distributed.launch, rank = local_rank
     args.rank = args.local_rank
+    # torchrun-era launchers export TORCHELASTIC_USE_AGENT_STORE=True, which makes torch's
+    # tcp:// rendezvous connect to the *launcher's* store as a client instead of letting
+    # rank 0 host one at --init-method's port: every rank would wait forever on a port
+    # nobody listens on.  The reference contract is "rendezvous at --init-method"
+    # (ref:167-168), so opt out of the agent store for this process.
+    os.environ.pop('TORCHELASTIC_USE_AGENT_STORE', None)
     from .runner import run
     return run(args)
 

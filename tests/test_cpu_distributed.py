@@ -1,0 +1,182 @@
+"""Multi-process CPU/gloo plumbing: DDP replacement vs stock DDP, both launch modes,
+checkpoint round trips against the reference's own code (BASELINE config 1)."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+TRAIN = os.path.join(ROOT, 'train.py')
+
+
+def _env():
+    env = dict(os.environ)
+    env['PYTHONPATH'] = ROOT + os.pathsep + env.get('PYTHONPATH', '')
+    for k in ('LOCAL_RANK', 'RANK', 'WORLD_SIZE', 'MASTER_ADDR', 'MASTER_PORT', 'TORCHELASTIC_RUN_ID'):
+        env.pop(k, None)
+    return env
+
+
+def _ddp_worker(rank, world, port, out_dir):
+    import pytorch_distributed_mnist_b200 as pdm
+    dist.init_process_group('gloo', init_method='tcp://127.0.0.1:{}'.format(port), world_size=world, rank=rank)
+    try:
+        torch.manual_seed(100 + rank)                      # different init per rank: broadcast must fix it
+        ours = pdm.DistributedDataParallel(pdm.CNN())
+        torch.manual_seed(100)                             # rank 0's init
+        stock_mod = pdm.CNN()
+        stock = torch.nn.parallel.DistributedDataParallel(stock_mod)
+        for a, b in zip(ours.module.parameters(), stock_mod.parameters()):
+            assert torch.equal(a, b), 'initial broadcast from rank 0 failed'
+        assert len(ours.buckets) >= 2
+        o_opt = pdm.FusedAdam(ours.parameters(), lr=1e-3)
+        s_opt = torch.optim.Adam(stock.parameters(), lr=1e-3)
+        ours.eval(); stock.eval()                          # dropout off: deterministic comparison
+        g = torch.Generator().manual_seed(7 + rank)
+        for _ in range(3):
+            x = torch.randn(8, 1, 28, 28, generator=g)
+            y = torch.randint(0, 10, (8,), generator=g)
+            for m, o in ((ours, o_opt), (stock, s_opt)):
+                loss = torch.nn.functional.cross_entropy(m(x), y)
+                o.zero_grad()
+                loss.backward()
+                o.step()
+        for a, b in zip(ours.module.parameters(), stock_mod.parameters()):
+            torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-6)
+        assert list(ours.state_dict().keys()) == list(stock.state_dict().keys())
+        assert ours.stats['bucket_launches'] == 3 * len(ours.buckets)
+        torch.save({k: v for k, v in ours.state_dict().items()}, os.path.join(out_dir, 'rank{}.pt'.format(rank)))
+        ours.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ddp_replacement_matches_stock_ddp_gloo(tmp_path, free_port):
+    mp.spawn(_ddp_worker, args=(2, free_port, str(tmp_path)), nprocs=2)
+    a = torch.load(str(tmp_path / 'rank0.pt'))
+    b = torch.load(str(tmp_path / 'rank1.pt'))
+    for k in a:
+        assert torch.equal(a[k], b[k]), 'replicas diverged: ' + k
+
+
+def _mismatch_worker(rank, world, port):
+    import pytorch_distributed_mnist_b200 as pdm
+    dist.init_process_group('gloo', init_method='tcp://127.0.0.1:{}'.format(port), world_size=world, rank=rank)
+    try:
+        model = pdm.Net() if rank == 0 else pdm.CNN()
+        with pytest.raises(RuntimeError, match='parameter shapes differ'):
+            pdm.DistributedDataParallel(model)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ddp_detects_mismatched_models(free_port):
+    mp.spawn(_mismatch_worker, args=(2, free_port), nprocs=2)
+
+
+COMMON = ['--backend', 'gloo', '--synthetic', '--train-size', '2048', '--test-size', '512', '--batch-size', '128',
+          '--workers', '3']
+
+
+def test_spawn_mode_train_resume_evaluate(tmp_path, free_port):
+    """way 2 (README:33) + resume (README:50-52) + evaluate (README:55-60) at W=2 on CPU."""
+    cwd = str(tmp_path)
+    url = 'tcp://127.0.0.1:{}'.format(free_port)
+    r = subprocess.run([sys.executable, TRAIN, '--world-size', '2', '--epochs', '2', '-i', url] + COMMON,
+                       cwd=cwd, env=_env(), capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stdout + r.stderr
+    out = r.stdout
+    assert out.count('rank: ') == 2 and 'rank: 1, device count: ' in out and 'workers:2' in out   # ceil(3/2)
+    assert out.count('Epoch: 1/2,') == 2                                  # every rank prints
+    assert os.path.isfile(os.path.join(cwd, 'checkpoints', 'checkpoint_0.pth.tar'))
+    assert os.path.isfile(os.path.join(cwd, 'checkpoints', 'checkpoint_1.pth.tar'))
+    assert os.path.isfile(os.path.join(cwd, 'checkpoints', 'model_best.pth.tar'))
+    ck = torch.load(os.path.join(cwd, 'checkpoints', 'checkpoint_1.pth.tar'))
+    assert ck['epoch'] == 2 and 0.0 <= ck['best_acc'] <= 1.0
+
+    r = subprocess.run([sys.executable, TRAIN, '--world-size', '2', '--epochs', '3', '-i', url, '--resume',
+                        'checkpoints/checkpoint_1.pth.tar'] + COMMON,
+                       cwd=cwd, env=_env(), capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "=> loaded checkpoint 'checkpoints/checkpoint_1.pth.tar' (epoch 2)" in r.stdout
+    assert 'Epoch: 2/3,' in r.stdout and 'Epoch: 1/3,' not in r.stdout
+
+    r = subprocess.run([sys.executable, TRAIN, '--world-size', '1', '-i', url, '--evaluate', '--resume',
+                        'checkpoints/model_best.pth.tar'] + COMMON,
+                       cwd=cwd, env=_env(), capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert 'test loss: ' in r.stdout and 'test acc: ' in r.stdout and '%.' in r.stdout
+
+    r = subprocess.run([sys.executable, TRAIN, '--world-size', '1', '-i', url, '--epochs', '0', '--resume',
+                        'nope.pth.tar'] + COMMON, cwd=cwd, env=_env(), capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0 and "=> no checkpoint found at 'nope.pth.tar'" in r.stdout
+
+
+def test_launch_mode_torch_distributed_launch(tmp_path, free_port):
+    """way 1 (README:19): torch.distributed.launch passes --local-rank=N."""
+    import socket
+    s = socket.socket(); s.bind(('127.0.0.1', 0)); mport = s.getsockname()[1]; s.close()
+    cmd = [sys.executable, '-m', 'torch.distributed.launch', '--nproc_per_node=2', '--master_addr', '127.0.0.1',
+           '--master_port', str(mport), TRAIN, '--world-size', '2', '--epochs', '1',
+           '-i', 'tcp://127.0.0.1:{}'.format(free_port)] + COMMON
+    r = subprocess.run(cmd, cwd=str(tmp_path), env=_env(), capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.count('Epoch: 0/1,') == 2
+    assert os.path.isfile(os.path.join(str(tmp_path), 'checkpoints', 'checkpoint_0.pth.tar'))
+
+
+def _ref_ckpt_worker(rank, world, port, path, ref_path):
+    """The SURVEY probe recipe: reference save_checkpoint + stock DDP + stock Adam."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location('ref_mod', ref_path)
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    dist.init_process_group('gloo', init_method='tcp://127.0.0.1:{}'.format(port), world_size=world, rank=rank)
+    try:
+        torch.manual_seed(0)
+        model = torch.nn.parallel.DistributedDataParallel(ref.Net())
+        opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+        for _ in range(3):
+            loss = torch.nn.functional.cross_entropy(model(torch.randn(16, 1, 28, 28)), torch.randint(0, 10, (16,)))
+            opt.zero_grad(); loss.backward(); opt.step()
+        os.chdir(path)
+        ref.save_checkpoint({'epoch': 4, 'state_dict': model.state_dict(), 'best_acc': 0.5,
+                             'optimizer': opt.state_dict()}, True, 3)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_reference_checkpoint_resumes_here_and_ours_loads_in_stock(tmp_path, free_port):
+    ref_path = '/root/reference/multi_proc_single_gpu.py'
+    if not os.path.isfile(ref_path):
+        ref_path = os.path.join(ROOT, 'baseline', '_ref', 'multi_proc_single_gpu.py')
+    if not os.path.isfile(ref_path):
+        pytest.skip('reference module not available')
+    mp.spawn(_ref_ckpt_worker, args=(1, free_port, str(tmp_path), ref_path), nprocs=1)
+    ck_path = os.path.join(str(tmp_path), 'checkpoints', 'checkpoint_3.pth.tar')
+    assert os.path.isfile(ck_path) and os.path.isfile(os.path.join(str(tmp_path), 'checkpoints', 'model_best.pth.tar'))
+    # reference checkpoint -> our CLI: evaluate, then resume training
+    r = subprocess.run([sys.executable, TRAIN, '--world-size', '1', '-i', 'tcp://127.0.0.1:{}'.format(free_port),
+                        '--evaluate', '--resume', ck_path] + COMMON,
+                       cwd=str(tmp_path), env=_env(), capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert 'best_acc: 0.5' in r.stdout and '(epoch 4)' in r.stdout and 'test acc: ' in r.stdout
+    r = subprocess.run([sys.executable, TRAIN, '--world-size', '1', '-i', 'tcp://127.0.0.1:{}'.format(free_port),
+                        '--epochs', '5', '--resume', ck_path] + COMMON,
+                       cwd=str(tmp_path), env=_env(), capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert 'Epoch: 4/5,' in r.stdout
+    # our checkpoint -> the stock stack (DDP(Net) + torch.optim.Adam), exactly as the reference would load it
+    ours = torch.load(os.path.join(str(tmp_path), 'checkpoints', 'checkpoint_4.pth.tar'))
+    theirs = torch.load(ck_path)
+    assert ours['epoch'] == 5
+    assert list(ours['state_dict'].keys()) == list(theirs['state_dict'].keys())
+    assert ours['optimizer']['state'][0]['step'].item() == theirs['optimizer']['state'][0]['step'].item() + 16
+    assert set(ours['optimizer']['param_groups'][0].keys()) == set(theirs['optimizer']['param_groups'][0].keys())
+    lin = torch.nn.Linear(784, 10)
+    lin.load_state_dict({k.replace('module.fc.', ''): v for k, v in ours['state_dict'].items()})
+    torch.optim.Adam(lin.parameters()).load_state_dict(ours['optimizer'])
