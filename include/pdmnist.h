@@ -151,6 +151,70 @@ int pdm_cross_entropy(const float* logits, const void* y, int y_dtype, int batch
                       pdm_stream_t stream);
 
 /* ------------------------------------------------------------------------
+ * tcgen05 / TMA GEMM at tf32 with fp32 accumulation (gemm_tcgen05.cu):
+ *     D[M,N] (+)= A[M,K] . B[N,K]^T
+ * The GEMM-shaped layers of the CNN extension: fc1 and, through
+ * the shifted-row implicit-GEMM modes, the 3x3 convolutions.  Replaces the
+ * cuBLAS / cuDNN calls the stock stack would make.
+ *  a, b      row-major fp32 matrices as stored: [a_rows][a_cols], pitch lda
+ *            (elements; base and pitch 16-byte aligned)
+ *  *_mn_major 0: stored [MN][K] (K contiguous); 1: stored [K][MN]
+ *  mode      0 plain GEMM
+ *            1 conv fwd/dgrad: A = NHWC activations as [pixels][C] (K-major);
+ *              k-block kb -> tap = kb / cblocks, A rows shifted by
+ *              shift_sign * ((tap/3)*img_w + tap%3); B = [N][taps*C] K-major
+ *            2 conv wgrad: A = dY [pixels][Cout] and B = X [pixels][Cin], both
+ *              MN-major; N = taps*Cin, column block j reads X shifted by its tap
+ *  epilogue  + bias[n], ReLU, zero where mask[m][n] <= 0; `accumulate` or
+ *            splits > 1 switches the store to atomic adds (d must be initialised)
+ * ---------------------------------------------------------------------- */
+typedef struct pdm_gemm_args {
+  const float* a; int64_t a_rows, a_cols, lda; int32_t a_mn_major;
+  const float* b; int64_t b_rows, b_cols, ldb; int32_t b_mn_major;
+  float* d; int64_t ldd;
+  int32_t M, N, K;
+  const float* bias; int32_t relu;
+  const float* mask; int64_t ld_mask;
+  int32_t block_n;      /* 0 = auto; multiple of 32, <= 256 */
+  int32_t splits;       /* split-K factor (0/1 = none) */
+  int32_t accumulate;
+  int32_t mode, img_w, cblocks, shift_sign;
+} pdm_gemm_args;
+int pdm_gemm_tf32(const pdm_gemm_args* args, pdm_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Non-GEMM CNN layers (cnn_kernels.cu), each fused with its neighbours.  The
+ * reference has no CNN; these serve the BASELINE.json extension
+ * and replace what cuDNN / ATen would run for it.  Activations are NHWC viewed
+ * as [B*26*26, C] (26-wide rows; conv2's valid outputs are the 24x24 corner).
+ * Dropout masks are Philox4x32-10(seed, element index) and are recomputed in
+ * the backward kernels, never stored.
+ * ---------------------------------------------------------------------- */
+/* conv1 1->c1 3x3 + bias + ReLU.  x [B,784] PDM_U8 (normalised in-kernel) or PDM_F32; w [c1][9]. */
+int pdm_conv1_fwd(const void* x, int x_dtype, const float* w, const float* bias, float* out,
+                  int batch, int c1, pdm_stream_t stream);
+/* dw [c1][9] += sum dz*x, db [c1] += sum dz   (dz already ReLU-masked). */
+int pdm_conv1_bwd(const void* x, int x_dtype, const float* dz, float* dw, float* db, int batch,
+                  int c1, pdm_stream_t stream);
+/* max-pool 2x2 + bias + ReLU + dropout(p) over raw conv accumulators z [B*676, C];
+ * out [B, C*144] in NCHW-flatten order; code [B*C*144] replay bytes for the backward. */
+int pdm_pool_fwd(const float* z, const float* bias, float* out, uint8_t* code, int batch, int C,
+                 float p, uint64_t seed, pdm_stream_t stream);
+/* dy [B*676, C] (fully written, zero outside the arg-max positions); dbias [C] += (may be NULL). */
+int pdm_pool_bwd(const float* dp, const uint8_t* code, float* dy, float* dbias, int batch, int C,
+                 float p, uint64_t seed, pdm_stream_t stream);
+/* logits [B,10] = dropout(h, p) . w^T + bias,  h [B,H], w [10][H]. */
+int pdm_fcout_fwd(const float* h, const float* w, const float* bias, float* logits, int batch,
+                  int H, float p, uint64_t seed, pdm_stream_t stream);
+/* dz1 [B,H] = (dl . w) * dropout * (h > 0); dw [10][H] +=, db [10] +=, db1 [H] += colsum(dz1). */
+int pdm_fcout_bwd(const float* dl, const float* h, const float* w, float* dz1, float* dw, float* db,
+                  float* db1, int batch, int H, float p, uint64_t seed, pdm_stream_t stream);
+/* z [rows][cols] = relu(z + bias[col]) in place (epilogue of a split-K GEMM). */
+int pdm_bias_relu(float* z, const float* bias, int64_t rows, int cols, pdm_stream_t stream);
+/* dir 0: w [Co][Ci][9] -> a [Co][9][Ci], b [Ci][9][Co] (b may be NULL);  dir 1: a [Co][Ci][9] += src [Co][9][Ci]. */
+int pdm_conv_relayout(const float* src, float* a, float* b, int cout, int cin, int dir, pdm_stream_t stream);
+
+/* ------------------------------------------------------------------------
  * Peer-memory communicator (comm.cu).  Replaces ProcessGroupNCCL + NCCL +
  * the c10d Reducer on the gradient path (ref:167-168, ref:188-189, ref:91;
  * SURVEY N2-N4, N7, K9, K14-K16).  One process per GPU; every rank allocates

@@ -112,6 +112,8 @@ def optional_decl(name):
     """Register argtypes for a symbol that newer builds of the library export."""
     def deco(fn):
         _OPTIONAL_DECLS[name] = fn
+        if _lib is not None and hasattr(_lib, name):
+            fn(getattr(_lib, name))
         return fn
     return deco
 

@@ -1,0 +1,202 @@
+"""CNN layer kernels vs stock PyTorch fp32 ops (tf32 tolerance on the GEMM-backed layers)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(out, ref, tol):
+    scale = ref.abs().max().item() + 1e-6
+    err = (out - ref).abs().max().item()
+    assert err <= tol * scale + 1e-6, 'max err {} vs scale {}'.format(err, scale)
+
+
+def _nhwc2d(t):          # [B,C,26,26] -> [B*676, C]
+    B, C = t.size(0), t.size(1)
+    return t.permute(0, 2, 3, 1).reshape(B * 676, C).contiguous()
+
+
+@pytest.mark.parametrize('batch,c1,dtype', [(3, 32, 'f32'), (5, 64, 'u8')])
+def test_conv1_forward_backward(batch, c1, dtype):
+    from pytorch_distributed_mnist_b200.ops.cnn_ops import Conv1Fn
+    torch.manual_seed(0)
+    xu = torch.randint(0, 256, (batch, 784), dtype=torch.uint8, device='cuda')
+    xf = xu.float().div(255).sub(0.1307).div(0.3081)
+    w = (torch.randn(c1, 1, 3, 3, device='cuda') * 0.3).requires_grad_(True)
+    b = torch.randn(c1, device='cuda').requires_grad_(True)
+    out = Conv1Fn.apply(xu if dtype == 'u8' else xf, w, b)
+    wr, br = w.detach().clone().requires_grad_(True), b.detach().clone().requires_grad_(True)
+    ref = F.relu(F.conv2d(xf.view(batch, 1, 28, 28), wr, br))
+    _rel(out, _nhwc2d(ref), 1e-5)
+    g = torch.randn_like(ref)
+    out.backward(_nhwc2d(g))
+    ref.backward(g)
+    _rel(w.grad, wr.grad, 1e-4)
+    _rel(b.grad, br.grad, 1e-4)
+
+
+@pytest.mark.parametrize('batch,c1,c2', [(2, 32, 64), (3, 64, 128)])
+def test_conv2_forward_backward(batch, c1, c2):
+    from pytorch_distributed_mnist_b200.ops.cnn_ops import Conv2Fn
+    torch.manual_seed(1)
+    a = torch.relu(torch.randn(batch, c1, 26, 26, device='cuda'))        # post-ReLU activations (some zeros)
+    a2d = _nhwc2d(a).requires_grad_(True)
+    w = (torch.randn(c2, c1, 3, 3, device='cuda') * 0.05).requires_grad_(True)
+    z = Conv2Fn.apply(a2d, w)
+    ar, wr = a.detach().clone().requires_grad_(True), w.detach().clone().requires_grad_(True)
+    ref = F.conv2d(ar, wr)
+    got = z.view(batch, 26, 26, c2)[:, :24, :24, :].permute(0, 3, 1, 2)
+    _rel(got, ref, 4e-3)
+    g = torch.randn_like(ref)
+    gfull = torch.zeros(batch, 26, 26, c2, device='cuda')
+    gfull[:, :24, :24, :] = g.permute(0, 2, 3, 1)
+    z.backward(gfull.view(batch * 676, c2))
+    ref.backward(g)
+    _rel(w.grad, wr.grad, 4e-3)
+    # the dgrad epilogue folds conv1's ReLU mask in: compare against grad * (a > 0)
+    _rel(a2d.grad, _nhwc2d(ar.grad * (a > 0)), 4e-3)
+
+
+@pytest.mark.parametrize('batch,C', [(2, 64), (3, 128)])
+def test_pool_bias_relu_forward_backward(batch, C):
+    from pytorch_distributed_mnist_b200.ops.cnn_ops import PoolFn
+    torch.manual_seed(2)
+    z = torch.randn(batch, C, 26, 26, device='cuda')
+    z2d = _nhwc2d(z).requires_grad_(True)
+    b = torch.randn(C, device='cuda').requires_grad_(True)
+    out = PoolFn.apply(z2d, b, 0.0, 0)
+    zr, br = z.detach().clone().requires_grad_(True), b.detach().clone().requires_grad_(True)
+    ref = F.max_pool2d(F.relu(zr[:, :, :24, :24] + br.view(1, C, 1, 1)), 2).flatten(1)
+    _rel(out, ref, 1e-6)
+    g = torch.randn_like(ref)
+    out.backward(g)
+    ref.backward(g)
+    _rel(z2d.grad, _nhwc2d(zr.grad), 1e-6)
+    _rel(b.grad, br.grad, 1e-4)
+
+
+def test_pool_dropout_mask_is_replayed_in_backward():
+    from pytorch_distributed_mnist_b200.ops.cnn_ops import PoolFn
+    torch.manual_seed(3)
+    z2d = (torch.rand(4 * 676, 64, device='cuda') + 0.5).requires_grad_(True)     # all positive: ReLU always live
+    b = torch.zeros(64, device='cuda')
+    out = PoolFn.apply(z2d, b, 0.25, 12345)
+    kept = (out != 0)
+    frac = kept.float().mean().item()
+    assert abs(frac - 0.75) < 0.02, frac
+    nz = out[kept]
+    pooled = F.max_pool2d(z2d.detach().view(4, 26, 26, 64).permute(0, 3, 1, 2)[:, :, :24, :24], 2).flatten(1)
+    torch.testing.assert_close(nz, pooled[kept] / 0.75, rtol=1e-6, atol=1e-6)
+    out.sum().backward()
+    # gradient reaches exactly one input per kept pooled element, scaled by 1/(1-p)
+    assert int((z2d.grad != 0).sum()) == int(kept.sum())
+    torch.testing.assert_close(z2d.grad[z2d.grad != 0], torch.full((int(kept.sum()),), 1 / 0.75, device='cuda'))
+    out2 = PoolFn.apply(z2d.detach(), b, 0.25, 12345)
+    assert torch.equal(out2, out.detach())                                        # same seed, same mask
+    out3 = PoolFn.apply(z2d.detach(), b, 0.25, 999)
+    assert not torch.equal(out3, out.detach())
+
+
+@pytest.mark.parametrize('batch,K,H', [(64, 9216, 128), (130, 1024, 96), (512, 9216, 128)])
+def test_fc1_forward_backward(batch, K, H):
+    from pytorch_distributed_mnist_b200.ops.cnn_ops import Fc1Fn
+    torch.manual_seed(4)
+    x = torch.randn(batch, K, device='cuda').requires_grad_(True)
+    w = (torch.randn(H, K, device='cuda') * 0.02).requires_grad_(True)
+    b = torch.randn(H, device='cuda').requires_grad_(True)
+    out = Fc1Fn.apply(x, w, b)
+    xr, wr, br = (t.detach().clone().requires_grad_(True) for t in (x, w, b))
+    ref = F.relu(F.linear(xr, wr, br))
+    _rel(out, ref, 4e-3)
+    g = torch.randn_like(ref)
+    out.backward(g)
+    ref.backward(g)
+    _rel(x.grad, xr.grad, 6e-3)
+    _rel(w.grad, wr.grad, 6e-3)
+    _rel(b.grad, br.grad, 1e-3)
+
+
+@pytest.mark.parametrize('batch,H', [(1, 128), (77, 128), (512, 1024)])
+def test_fcout_forward_backward(batch, H):
+    from pytorch_distributed_mnist_b200.ops.cnn_ops import FcOutFn
+    torch.manual_seed(5)
+    h = torch.relu(torch.randn(batch, H, device='cuda')).requires_grad_(True)
+    w = (torch.randn(10, H, device='cuda') * 0.1).requires_grad_(True)
+    b = torch.randn(10, device='cuda').requires_grad_(True)
+    out = FcOutFn.apply(h, w, b, 0.0, 0)
+    hr, wr, br = (t.detach().clone().requires_grad_(True) for t in (h, w, b))
+    ref = F.linear(hr, wr, br)
+    _rel(out, ref, 1e-5)
+    g = torch.randn_like(ref)
+    out.backward(g)
+    ref.backward(g)
+    _rel(h.grad, hr.grad * (hr.detach() > 0), 1e-5)          # ReLU mask of the producer is folded in
+    _rel(w.grad, wr.grad, 1e-4)
+    _rel(b.grad, br.grad, 1e-4)
+
+
+def test_fcout_dropout_consistency():
+    from pytorch_distributed_mnist_b200.ops.cnn_ops import FcOutFn
+    torch.manual_seed(6)
+    h = (torch.rand(256, 128, device='cuda') + 0.1).requires_grad_(True)
+    w = torch.ones(10, 128, device='cuda', requires_grad=True)
+    b = torch.zeros(10, device='cuda', requires_grad=True)
+    out = FcOutFn.apply(h, w, b, 0.5, 777)
+    out[:, 0].sum().backward()
+    kept = h.grad != 0
+    assert abs(kept.float().mean().item() - 0.5) < 0.02
+    torch.testing.assert_close(h.grad[kept], torch.full((int(kept.sum()),), 2.0, device='cuda'))
+    torch.testing.assert_close(out[:, 0], (h.detach() * kept * 2.0).sum(1), rtol=1e-5, atol=1e-4)
+
+
+def test_cnn_module_matches_stock_ops_end_to_end():
+    """The whole CNN on the native kernels vs the same module on stock PyTorch ops (eval mode:
+    dropout off), forward logits and every parameter gradient."""
+    import pytorch_distributed_mnist_b200 as pdm
+    from pytorch_distributed_mnist_b200.ops import cnn_ops
+    assert cnn_ops.available()
+    torch.manual_seed(7)
+    model = pdm.CNN().cuda().eval()
+    ref = pdm.CNN().cuda().eval()
+    ref.load_state_dict(model.state_dict())
+    x = torch.randn(48, 1, 28, 28, device='cuda')
+    y = torch.randint(0, 10, (48,), device='cuda')
+    logits = model(x)
+    loss = F.cross_entropy(logits, y)
+    loss.backward()
+    # reference path: stock ops (same module code the CPU uses)
+    r = F.relu(ref.conv1(x))
+    r = F.max_pool2d(F.relu(ref.conv2(r)), 2).flatten(1)
+    r = ref.fc2(F.relu(ref.fc1(r)))
+    rloss = F.cross_entropy(r, y)
+    rloss.backward()
+    _rel(logits, r, 1e-2)
+    assert abs(loss.item() - rloss.item()) < 1e-2
+    for (n, p), (_, q) in zip(model.named_parameters(), ref.named_parameters()):
+        _rel(p.grad, q.grad, 2e-2)
+
+
+def test_cnn_trains_on_synthetic_data():
+    import pytorch_distributed_mnist_b200 as pdm
+    from pytorch_distributed_mnist_b200.data import mnist
+    torch.manual_seed(8)
+    images, labels = mnist.synthetic_mnist(True, size=4096)
+    x = torch.from_numpy(images).cuda().view(-1, 784)
+    y = torch.from_numpy(labels).cuda().long()
+    model = pdm.CNN().cuda().train()
+    opt = pdm.FusedAdam(model.parameters(), lr=1e-3)
+    losses = []
+    for ep in range(2):
+        for i in range(0, 4096, 128):
+            logits = model(x[i:i + 128])                    # uint8 in: normalised inside conv1
+            loss = F.cross_entropy(logits, y[i:i + 128])
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+            losses.append(loss.item())
+    assert sum(losses[-8:]) / 8 < 0.5 * sum(losses[:8]) / 8
+    model.eval()
+    with torch.no_grad():
+        acc = (model(x[:1024]).argmax(1) == y[:1024]).float().mean().item()
+    assert acc > 0.8

@@ -1,0 +1,84 @@
+"""tcgen05/TMA tf32 GEMM vs torch fp32 matmul (tf32 tolerance: inputs carry 10 mantissa bits)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _close(out, ref, k):
+    # tf32 truncation: relative error ~2^-10 per product, random-walk over k terms
+    scale = ref.abs().max().item() + 1e-6
+    err = (out - ref).abs().max().item()
+    assert err <= 4e-3 * scale + 1e-5, 'max err {} vs scale {} (k={})'.format(err, scale, k)
+
+
+@pytest.mark.parametrize('M,N,K', [(128, 64, 32), (128, 128, 128), (512, 128, 9216), (300, 200, 100), (129, 33, 40),
+                                   (1024, 256, 512)])
+@pytest.mark.parametrize('a_mn,b_mn', [(False, False), (False, True), (True, True), (True, False)])
+def test_gemm_all_major_modes(M, N, K, a_mn, b_mn):
+    from pytorch_distributed_mnist_b200.ops.gemm import gemm
+    if (a_mn and M % 4) or (b_mn and N % 4) or ((not a_mn or not b_mn) and K % 4):
+        pytest.skip('row pitch must be 16-byte aligned')
+    torch.manual_seed(0)
+    A = torch.randn(M, K, device='cuda')
+    B = torch.randn(N, K, device='cuda')
+    a = A.t().contiguous() if a_mn else A
+    b = B.t().contiguous() if b_mn else B
+    out = gemm(a, b, a_mn_major=a_mn, b_mn_major=b_mn)
+    _close(out, A @ B.t(), K)
+
+
+@pytest.mark.parametrize('block_n', [32, 64, 128, 256])
+def test_gemm_block_n_and_epilogue(block_n):
+    from pytorch_distributed_mnist_b200.ops.gemm import gemm
+    torch.manual_seed(1)
+    A, B = torch.randn(256, 96, device='cuda'), torch.randn(256, 96, device='cuda')
+    bias = torch.randn(256, device='cuda')
+    mask = torch.randn(256, 256, device='cuda')
+    out = gemm(A, B, bias=bias, relu=True, mask=mask, block_n=block_n)
+    ref = torch.relu(A @ B.t() + bias) * (mask > 0)
+    _close(out, ref, 96)
+
+
+@pytest.mark.parametrize('splits', [2, 5])
+def test_gemm_split_k_and_accumulate(splits):
+    from pytorch_distributed_mnist_b200.ops.gemm import gemm
+    torch.manual_seed(2)
+    A, B = torch.randn(128, 2048, device='cuda'), torch.randn(96, 2048, device='cuda')
+    out = gemm(A.t().contiguous(), B.t().contiguous(), a_mn_major=True, b_mn_major=True, splits=splits)
+    _close(out, A @ B.t(), 2048)
+    base = torch.ones(128, 96, device='cuda')
+    gemm(A, B, out=base, accumulate=True)
+    _close(base, A @ B.t() + 1, 2048)
+
+
+@pytest.mark.parametrize('batch,cin,cout', [(2, 32, 64), (5, 64, 32), (3, 32, 32)])
+def test_conv3x3_forward_dgrad_wgrad(batch, cin, cout):
+    """Shifted-row implicit GEMM vs F.conv2d and its autograd (26x26 -> 24x24 like conv2)."""
+    from pytorch_distributed_mnist_b200.ops import gemm as G
+    H = W = 26
+    torch.manual_seed(3)
+    x = torch.randn(batch, cin, H, W, device='cuda', requires_grad=True)
+    w = (torch.randn(cout, cin, 3, 3, device='cuda') * 0.1).requires_grad_(True)
+    y = F.conv2d(x, w)
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    # NHWC activations as [B*H*W, C]; weights as [Cout][tap][Cin]
+    x2d = x.detach().permute(0, 2, 3, 1).reshape(batch * H * W, cin).contiguous()
+    wk = w.detach().permute(0, 2, 3, 1).reshape(cout, 9 * cin).contiguous()
+    out = G.gemm(x2d, wk, mode=G.MODE_CONV, img_w=W, cblocks=cin // 32, shift_sign=1, M=batch * H * W, N=cout, K=9 * cin)
+    got = out.view(batch, H, W, cout)[:, :H - 2, :W - 2, :].permute(0, 3, 1, 2)
+    _close(got, y.detach(), 9 * cin)
+    # dgrad: dX[q] = sum_tap dY[q - shift(tap)] . W[tap]   with dY zero at the invalid positions
+    gy_full = torch.zeros(batch, H, W, cout, device='cuda')
+    gy_full[:, :H - 2, :W - 2, :] = gy.permute(0, 2, 3, 1)
+    gy2d = gy_full.view(batch * H * W, cout)
+    wd = w.detach().permute(1, 2, 3, 0).reshape(cin, 9 * cout).contiguous()      # [Cin][tap][Cout]
+    dx = G.gemm(gy2d, wd, mode=G.MODE_CONV, img_w=W, cblocks=cout // 32, shift_sign=-1, M=batch * H * W, N=cin, K=9 * cout)
+    _close(dx.view(batch, H, W, cin).permute(0, 3, 1, 2), x.grad, 9 * cout)
+    # wgrad: dW[cout][tap][cin] = sum_q dY[q][cout] * X[q + shift(tap)][cin]
+    dw = G.gemm(gy2d, x2d, a_mn_major=True, b_mn_major=True, mode=G.MODE_WGRAD, img_w=W, cblocks=cin // 32,
+                M=cout, N=9 * cin, K=batch * H * W, splits=4)
+    ref_dw = w.grad.permute(0, 2, 3, 1).reshape(cout, 9 * cin)
+    _close(dw, ref_dw, batch * 576)

@@ -1,0 +1,208 @@
+"""Multi-GPU checks of the peer-memory communicator: run with
+`pytest -m gpu` on a box with >= 2 GPUs (gpurun --gpus 2); skipped otherwise.
+
+One process per GPU (mp.spawn), NCCL process group for the plumbing and as the oracle."""
+import os
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+
+MEAN, STD = 0.1307, 0.3081
+
+
+def _world():
+    n = torch.cuda.device_count()
+    return 8 if n >= 8 else (4 if n >= 4 else 2)
+
+
+def _init(rank, world, port):
+    torch.cuda.set_device(rank)
+    dist.init_process_group('nccl', init_method='tcp://127.0.0.1:{}'.format(port), world_size=world, rank=rank,
+                            device_id=torch.device('cuda', rank))
+
+
+def _rand(seed, n):
+    return torch.randn(n, generator=torch.Generator().manual_seed(seed))
+
+
+def _comm_worker(rank, world, port):
+    from pytorch_distributed_mnist_b200.ops import _lib
+    from pytorch_distributed_mnist_b200.parallel.peer import PeerComm
+    _init(rank, world, port)
+    try:
+        assert PeerComm.supported(world)
+        dev = torch.device('cuda', rank)
+        sizes = [4, 1024, 7852, 300000, 1 << 20]
+        nmax = max(sizes)
+        comm = PeerComm(rank, world, dev, data_bytes=nmax * 4 * 5 + 8192)
+        a, b, p, m, v = (comm.data_tensor(nmax) for _ in range(5))
+        comm.barrier()
+        # broadcast from every root
+        for root in range(world):
+            a.copy_(_rand(100 + rank, nmax))
+            torch.cuda.synchronize()
+            comm.broadcast(a, root=root)
+            torch.cuda.synchronize()
+            assert torch.equal(a.cpu(), _rand(100 + root, nmax)), 'broadcast root {}'.format(root)
+        # plain all-reduce, both algorithms, bitwise vs the rank-ordered fp32 sum
+        for n in sizes:
+            for algo in (1, 2):
+                for rep in range(2):
+                    a[:n].copy_(_rand(1000 * rep + 10 * n % 997 + rank, n))
+                    b[:n].zero_()
+                    torch.cuda.synchronize()
+                    dst = b[:n] if algo == 1 else a[:n]
+                    comm.allreduce(a[:n], dst, average=True, algo=algo)
+                    torch.cuda.synchronize()
+                    exp = torch.zeros(n)
+                    for r in range(world):
+                        exp = exp + _rand(1000 * rep + 10 * n % 997 + r, n)
+                    exp = exp * (1.0 / world)
+                    assert torch.equal(dst.cpu(), exp), 'allreduce n={} algo={} rep={}'.format(n, algo, rep)
+        # fused all-reduce + Adam: vs torch on the averaged gradient; replicas bit-identical
+        for n, algo in ((7852, 1), (300000, 2), (1 << 20, 2)):
+            p[:n].copy_(_rand(5, n))
+            m[:n].zero_()
+            v[:n].zero_()
+            ref_p = _rand(5, n).cuda().requires_grad_(True)
+            ropt = torch.optim.Adam([ref_p], lr=1e-2)
+            for t in range(1, 4):
+                a[:n].copy_(_rand(7000 + 10 * t + rank, n))
+                torch.cuda.synchronize()
+                h = _lib.Hyper(opt=_lib.PDM_OPT_ADAM, lr=1e-2, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0, step=t)
+                comm.allreduce_optim(a[:n], p[:n], m[:n], v[:n], h, algo=algo)
+                torch.cuda.synchronize()
+                g = torch.zeros(n)
+                for r in range(world):
+                    g = g + _rand(7000 + 10 * t + r, n)
+                ref_p.grad = (g * (1.0 / world)).cuda()
+                ropt.step()
+            torch.testing.assert_close(p[:n], ref_p.detach(), rtol=1e-5, atol=1e-6)
+            mine = p[:n].clone()
+            others = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(others, mine)
+            for o in others:
+                assert torch.equal(o, mine), 'replicas diverged (n={}, algo={})'.format(n, algo)
+        assert comm.status() == 0
+        comm.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_comm_broadcast_allreduce_fused_optimizer(free_port):
+    mp.spawn(_comm_worker, args=(_world(), free_port), nprocs=_world())
+
+
+def _net_worker(rank, world, port):
+    import torch.nn.functional as F
+    from pytorch_distributed_mnist_b200 import Net, FusedAdam, DistributedDataParallel
+    from pytorch_distributed_mnist_b200.ops.fused_step import NetStepper
+    _init(rank, world, port)
+    try:
+        dev = torch.device('cuda', rank)
+        torch.manual_seed(50 + rank)
+        model = DistributedDataParallel(Net().to(dev), device_ids=[rank])
+        assert model.uses_peer
+        opt = FusedAdam(model.parameters(), lr=1e-3)
+        st = NetStepper(dev, comm=model.comm)
+        # oracle: stock DDP + Adam from the same (broadcast) init
+        ref = torch.nn.Linear(784, 10).to(dev)
+        ref.load_state_dict(model.module.fc.state_dict())
+        ref = torch.nn.parallel.DistributedDataParallel(ref, device_ids=[rank])
+        ropt = torch.optim.Adam(ref.parameters(), lr=1e-3)
+        for t in range(1, 26):
+            B = 64 if t % 5 else 24
+            g = torch.Generator().manual_seed(1000 * t + rank)
+            x = torch.randint(0, 256, (B, 784), generator=g, dtype=torch.uint8).to(dev)
+            y = torch.randint(0, 10, (B,), generator=g).to(dev)
+            st.train_step(x, y, opt.flat.params, opt.flat.exp_avg, opt.flat.exp_avg_sq, opt.hyper(t))
+            loss = F.cross_entropy(ref(x.float().div(255).sub(MEAN).div(STD)), y)
+            ropt.zero_grad()
+            loss.backward()
+            ropt.step()
+        torch.cuda.synchronize()
+        torch.testing.assert_close(model.module.fc.weight.detach(), ref.module.weight.detach(), rtol=1e-3, atol=2e-4)
+        mine = opt.flat.params.clone()
+        others = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(others, mine)
+        for o in others:
+            assert torch.equal(o, mine), 'replicas diverged in the fused LL step'
+        model.comm.check_status()
+        model.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_fused_net_step_ll_allreduce(free_port):
+    mp.spawn(_net_worker, args=(_world(), free_port), nprocs=_world())
+
+
+def _cnn_worker(rank, world, port):
+    import pytorch_distributed_mnist_b200 as pdm
+    _init(rank, world, port)
+    try:
+        dev = torch.device('cuda', rank)
+        torch.manual_seed(7 + rank)
+        ours = pdm.DistributedDataParallel(pdm.CNN().to(dev), device_ids=[rank])
+        assert ours.uses_peer and len(ours.buckets) >= 2
+        torch.manual_seed(7)
+        stock_mod = pdm.CNN().to(dev)
+        stock = torch.nn.parallel.DistributedDataParallel(stock_mod, device_ids=[rank])
+        for a, b in zip(ours.module.parameters(), stock_mod.parameters()):
+            assert torch.equal(a, b), 'peer broadcast from rank 0 failed'
+        o_opt = pdm.FusedAdam(ours.parameters(), lr=1e-3)
+        s_opt = torch.optim.Adam(stock.parameters(), lr=1e-3)
+        ours.eval(); stock.eval()
+        g = torch.Generator().manual_seed(70 + rank)
+        for _ in range(4):
+            x = torch.randn(32, 1, 28, 28, generator=g).to(dev)
+            y = torch.randint(0, 10, (32,), generator=g).to(dev)
+            for m, o in ((ours, o_opt), (stock, s_opt)):
+                loss = torch.nn.functional.cross_entropy(m(x), y)
+                o.zero_grad()
+                loss.backward()
+                o.step()
+        torch.cuda.synchronize()
+        for a, b in zip(ours.module.parameters(), stock_mod.parameters()):
+            torch.testing.assert_close(a, b, rtol=2e-3, atol=2e-5)
+        mine = ours.flat.params.clone()
+        others = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(others, mine)
+        for o in others:
+            assert torch.equal(o, mine), 'replicas diverged in the bucketed fused path'
+        assert o_opt.step_count == 4
+        ours.comm.check_status()
+        ours.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_bucketed_fused_allreduce_optimizer_cnn(free_port):
+    mp.spawn(_cnn_worker, args=(_world(), free_port), nprocs=_world())
+
+
+def _run_worker(rank, world, port, out_dir):
+    from pytorch_distributed_mnist_b200.cli import build_parser
+    from pytorch_distributed_mnist_b200 import runner
+    args = build_parser().parse_args(['--world-size', str(world), '--synthetic', '--train-size', '8192', '--test-size',
+                                      '2048', '--batch-size', str(64 * world), '--epochs', '2', '-i',
+                                      'tcp://127.0.0.1:{}'.format(port), '--checkpoint-dir', out_dir])
+    args.rank = rank
+    out = runner.run(args)
+    torch.save(out['history'], os.path.join(out_dir, 'hist{}.pt'.format(rank)))
+
+
+def test_full_job_spawn_nccl_peer(tmp_path, free_port):
+    """BASELINE config 2 in miniature: Net, batch 64/GPU, mp.spawn-style ranks, peer path."""
+    world = _world()
+    mp.spawn(_run_worker, args=(world, free_port, str(tmp_path)), nprocs=world)
+    hists = [torch.load(str(tmp_path / 'hist{}.pt'.format(r))) for r in range(world)]
+    for h in hists:
+        assert h[1]['test_acc'] > 0.85
+        # every rank evaluates the full test set with identical parameters
+        assert h[1]['test_acc'] == hists[0][1]['test_acc'] and abs(h[1]['test_loss'] - hists[0][1]['test_loss']) < 1e-9
+    assert os.path.isfile(str(tmp_path / 'checkpoint_1.pth.tar'))
