@@ -19,7 +19,9 @@
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
+#include <memory>
 #include <mutex>
+#include <stdlib.h>
 #include <new>
 #include <thread>
 #include <vector>
@@ -36,7 +38,16 @@ struct Job {              // one run() call, shared with the workers
   int64_t count = 0;
   int batch = 0;
   int64_t nsteps = 0;
+  std::atomic<int64_t> next{0};   // next batch index to stage (per job: a late worker of an
+                                  // earlier job can never claim a batch of this one)
 };
+
+bool debug_on() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("PDM_ENGINE_DEBUG"); v = (e && *e && *e != '0') ? 1 : 0; }
+  return v == 1;
+}
+#define DBG(...) do { if (debug_on()) { fprintf(stderr, "[pdm_engine] " __VA_ARGS__); fputc('\n', stderr); fflush(stderr); } } while (0)
 
 }  // namespace
 
@@ -73,8 +84,7 @@ struct pdm_engine {
   std::condition_variable cv_work, cv_filled, cv_free;
   bool quit = false;
   uint64_t job_id = 0;
-  Job job;
-  std::atomic<int64_t> next_batch{0};
+  std::shared_ptr<Job> job;
   std::vector<int64_t> filled_batch;      // per slot: batch index staged there (-1 = none)
   std::vector<int64_t> free_for;          // per slot: first batch index allowed to overwrite it
   int64_t workers_active = 0;
@@ -83,6 +93,7 @@ struct pdm_engine {
 namespace {
 
 void gather_batch(pdm_engine* e, const Job& job, int64_t b, uint8_t* dst) {
+  DBG("worker stages batch %lld", (long long)b);
   const int64_t lo = b * job.batch;
   const int64_t n = std::min<int64_t>(job.batch, job.count - lo);
   uint8_t* img = dst;
@@ -101,17 +112,18 @@ void gather_batch(pdm_engine* e, const Job& job, int64_t b, uint8_t* dst) {
 void worker_main(pdm_engine* e) {
   uint64_t seen = 0;
   for (;;) {
-    Job job;
+    std::shared_ptr<Job> jp;
     {
       std::unique_lock<std::mutex> lk(e->mu);
       e->cv_work.wait(lk, [&] { return e->quit || e->job_id != seen; });
       if (e->quit) return;
       seen = e->job_id;
-      job = e->job;
+      jp = e->job;
       e->workers_active += 1;
     }
+    Job& job = *jp;
     for (;;) {
-      const int64_t b = e->next_batch.fetch_add(1);
+      const int64_t b = job.next.fetch_add(1);
       if (b >= job.nsteps) break;
       const int s = (int)(b % e->slots);
       {
@@ -246,16 +258,18 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
     int rc = ensure_results(e, nsteps);
     if (rc != PDM_OK) return rc;
   }
+  std::shared_ptr<Job> job = std::make_shared<Job>();
+  job->indices = indices;
+  job->count = count;
+  job->batch = batch;
+  job->nsteps = nsteps;
   {
     std::lock_guard<std::mutex> lk(e->mu);
-    e->job.indices = indices;
-    e->job.count = count;
-    e->job.batch = batch;
-    e->job.nsteps = nsteps;
-    e->next_batch.store(0);
+    e->job = job;
     for (int s = 0; s < e->slots; ++s) { e->filled_batch[s] = -1; e->free_for[s] = 0; }
     e->job_id += 1;
   }
+  DBG("run: %lld steps of batch %d (train=%d)", (long long)nsteps, batch, train);
   e->cv_work.notify_all();
 
   // both streams start after everything already queued on the device
@@ -275,6 +289,7 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
       std::unique_lock<std::mutex> lk(e->mu);
       e->cv_filled.wait(lk, [&] { return e->filled_batch[s] == b; });
     }
+    DBG("main issues step %lld (slot %d, n=%d)", (long long)b, s, n);
     const size_t bytes = (size_t)n * kSample;
     cudaError_t ce = cudaMemcpyAsync(e->dev_slot[s], e->host_slot[s], bytes, cudaMemcpyHostToDevice, st);
     if (ce == cudaSuccess) ce = cudaEventRecord(e->h2d_done[s], st);
@@ -344,11 +359,12 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
     // release the workers before reporting the failure
     {
       std::lock_guard<std::mutex> lk(e->mu);
-      e->next_batch.store(nsteps);
+      job->next.store(nsteps);
       for (int s = 0; s < e->slots; ++s) e->free_for[s] = 0;
     }
     e->cv_free.notify_all();
   }
+  DBG("all steps issued, draining streams");
   cudaStreamWaitEvent(e->stream[0], e->kernel_done[1], 0);
   cudaStreamSynchronize(e->stream[1]);
   cudaEventRecord(e->ev_end, e->stream[0]);
@@ -357,8 +373,9 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
     std::unique_lock<std::mutex> lk(e->mu);
     for (int s = 0; s < e->slots; ++s) e->free_for[s] = 0;
     e->cv_free.notify_all();
-    e->cv_filled.wait(lk, [&] { return e->workers_active == 0 && e->next_batch.load() >= nsteps; });
+    e->cv_filled.wait(lk, [&] { return e->workers_active == 0 && job->next.load() >= nsteps; });
   }
+  DBG("run done");
   if (rc != PDM_OK) return rc;
   if (se != cudaSuccess) {
     pdm_set_error("pdm_engine_run: device error after %lld steps -> %s", (long long)nsteps, cudaGetErrorString(se));
