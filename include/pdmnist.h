@@ -249,6 +249,21 @@ int pdm_comm_allreduce_optim(pdm_comm* c, size_t grad_off, size_t out_off, size_
 int pdm_comm_destroy(pdm_comm* c);
 
 /* ------------------------------------------------------------------------
+ * TCP key-value rendezvous store (store.cu; host code only).  The role of the
+ * c10d TCPStore behind the reference's tcp:// init method (ref:167-168,
+ * ref:323-327) as far as this framework needs it: publishing the
+ * communicator's IPC handles and counting arrivals.  The rank with is_server
+ * hosts the store on `port`; every rank connects as a client.
+ * ---------------------------------------------------------------------- */
+typedef struct pdm_store pdm_store;
+int pdm_store_create(pdm_store** out, const char* host, int port, int is_server, double timeout_s);
+int pdm_store_set(pdm_store* s, const char* key, const void* val, size_t len);
+/* Blocks until `key` exists (or timeout).  *len = value size; at most cap bytes copied. */
+int pdm_store_get(pdm_store* s, const char* key, void* buf, size_t cap, size_t* len);
+int pdm_store_add(pdm_store* s, const char* key, int64_t delta, int64_t* result);
+int pdm_store_destroy(pdm_store* s);
+
+/* ------------------------------------------------------------------------
  * Native epoch executor for the fused Net path (engine.cu).  Replaces the
  * DataLoader worker processes, the per-step pageable H2D copies and the two
  * per-step host syncs of Trainer.train()/evaluate() (ref:77-116; SURVEY N13,

@@ -68,6 +68,9 @@ def build_parser():
     parser.add_argument('--device', choices=('auto', 'cuda', 'cpu'), default='auto')
     parser.add_argument('--comm', choices=('auto', 'peer', 'group'), default='auto',
                         help='gradient path: peer = our NVLink peer-memory kernels, group = torch.distributed')
+    parser.add_argument('--store', choices=('torch', 'native'), default='torch',
+                        help='key-value store for the peer-memory bootstrap: the process group\'s TCPStore, or '
+                             'our native TCP store on the port after --init-method\'s')
     parser.add_argument('--fused', choices=('auto', 'on', 'off'), default='auto',
                         help='fused single-kernel training step for the reference Net')
     parser.add_argument('--checkpoint-dir', type=str, default=None, help='default: ./checkpoints (ref:264)')

@@ -86,7 +86,7 @@ struct pdm_engine {
   uint64_t job_id = 0;
   std::shared_ptr<Job> job;
   std::vector<int64_t> filled_batch;      // per slot: batch index staged there (-1 = none)
-  std::vector<int64_t> free_for;          // per slot: first batch index allowed to overwrite it
+  std::vector<int64_t> free_for;          // per slot: highest batch index allowed to be staged there
   int64_t workers_active = 0;
 };
 
@@ -128,7 +128,7 @@ void worker_main(pdm_engine* e) {
       const int s = (int)(b % e->slots);
       {
         std::unique_lock<std::mutex> lk(e->mu);
-        e->cv_free.wait(lk, [&] { return e->quit || e->free_for[s] <= b; });
+        e->cv_free.wait(lk, [&] { return e->quit || b <= e->free_for[s]; });
         if (e->quit) break;
       }
       gather_batch(e, job, b, e->host_slot[s]);
@@ -266,7 +266,7 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
   {
     std::lock_guard<std::mutex> lk(e->mu);
     e->job = job;
-    for (int s = 0; s < e->slots; ++s) { e->filled_batch[s] = -1; e->free_for[s] = 0; }
+    for (int s = 0; s < e->slots; ++s) { e->filled_batch[s] = -1; e->free_for[s] = s; }
     e->job_id += 1;
   }
   DBG("run: %lld steps of batch %d (train=%d)", (long long)nsteps, batch, train);
@@ -360,7 +360,7 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
     {
       std::lock_guard<std::mutex> lk(e->mu);
       job->next.store(nsteps);
-      for (int s = 0; s < e->slots; ++s) e->free_for[s] = 0;
+      for (int s = 0; s < e->slots; ++s) e->free_for[s] = INT64_MAX;
     }
     e->cv_free.notify_all();
   }
@@ -371,7 +371,7 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
   cudaError_t se = cudaStreamSynchronize(e->stream[0]);
   {
     std::unique_lock<std::mutex> lk(e->mu);
-    for (int s = 0; s < e->slots; ++s) e->free_for[s] = 0;
+    for (int s = 0; s < e->slots; ++s) e->free_for[s] = INT64_MAX;
     e->cv_free.notify_all();
     e->cv_filled.wait(lk, [&] { return e->workers_active == 0 && job->next.load() >= nsteps; });
   }

@@ -18,9 +18,12 @@
 // Operand layouts.  Each operand is a row-major fp32 matrix in global memory, used either
 //   K-major  : stored [MN][K]  -> one TMA box  {32 k (=128 B), rows}  per stage
 //   MN-major : stored [K][MN]  -> MN/32 boxes  {32 mn (=128 B), 32 k} per stage ("atoms")
-// both with CU_TENSOR_MAP_SWIZZLE_128B; the UMMA shared-memory descriptors use the matching
-// SWIZZLE_128B canonical layouts (K-major: SBO = 1024 B; MN-major: SBO = 1024 B,
-// LBO = 4096 B = atom stride), so no transposed copy of an activation or a weight is ever made.
+// K-major tiles use CU_TENSOR_MAP_SWIZZLE_128B and the UMMA SWIZZLE_128B canonical layout
+// (8 rows x 128 B atoms, SBO = 1024 B).  MN-major tf32 has exactly one legal layout on
+// sm_100: 128-byte swizzle with 32-byte atomicity -- CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B on
+// the TMA side, UMMA layout type SWIZZLE_128B_BASE32B (4 k-rows x 128 B atoms, SBO = 512 B,
+// LBO = 4096 B = stride between 32-wide MN atoms).  Either way the operand is consumed in the
+// layout it already has: no transposed copy of an activation or a weight is ever made.
 //
 // Implicit-GEMM convolution (3x3, stride 1, no padding) uses NHWC activations viewed as a 2-D
 // matrix [B*H*W, C] and the identity  in_pixel(q, tap) = q + kh*W + kw : the A tile of filter
@@ -31,6 +34,7 @@
 #include "common.cuh"
 
 #include <cuda.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -60,6 +64,7 @@ struct Params {
   int relu, atomic;
   uint32_t idesc;
   uint32_t tmem_cols;
+  uint32_t mn_layout, mn_sbo, mn_lbo;   // UMMA descriptor fields for MN-major operands
 };
 
 // ---------------------------------------------------------------------------- PTX wrappers
@@ -121,13 +126,13 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
 
 // UMMA shared-memory descriptor, SWIZZLE_128B, sm_100 version field = 1.
 //   bits [0,14) start address >> 4, [16,30) LBO >> 4, [32,46) SBO >> 4, [46,48) version, [61,64) layout type (2 = SW128)
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout = 2) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr >> 4) & 0x3FFF);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
+  d |= (uint64_t)(layout & 7u) << 61;
   return d;
 }
 
@@ -217,8 +222,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
         for (int k = 0; k < kBlockK / kUmmaK; ++k) {
           // K-major: next 8 k = +32 bytes inside the swizzle atom.  MN-major: next 8 k-rows = +1024 bytes.
-          const uint64_t da = p.a_mn ? make_desc(sa + k * 1024, kAtomBytes, 1024) : make_desc(sa + k * 32, 0, 1024);
-          const uint64_t db = p.b_mn ? make_desc(sb + k * 1024, kAtomBytes, 1024) : make_desc(sb + k * 32, 0, 1024);
+          const uint64_t da = p.a_mn ? make_desc(sa + k * 1024, p.mn_lbo, p.mn_sbo, p.mn_layout) : make_desc(sa + k * 32, 0, 1024);
+          const uint64_t db = p.b_mn ? make_desc(sb + k * 1024, p.mn_lbo, p.mn_sbo, p.mn_layout) : make_desc(sb + k * 32, 0, 1024);
           umma_tf32(tmem_base, da, db, p.idesc, (i | k) != 0 ? 1u : 0u);
         }
         umma_commit(empty + s);        // stage reusable once these MMAs have read it
@@ -276,7 +281,12 @@ EncodeFn get_encode() {
 }
 
 // 2-D fp32 row-major matrix [rows][cols] with leading dimension ld (elements); box = {32 cols, box_rows}.
-int make_map(CUtensorMap* map, const float* base, long long rows, long long cols, long long ld, int box_rows) {
+int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return (e && *e) ? atoi(e) : dflt;
+}
+
+int make_map(CUtensorMap* map, const float* base, long long rows, long long cols, long long ld, int box_rows, int mn_major) {
   EncodeFn enc = get_encode();
   PDM_REQUIRE(enc != nullptr, PDM_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
   PDM_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 4) % 16 == 0, PDM_ERR_ARG,
@@ -285,8 +295,11 @@ int make_map(CUtensorMap* map, const float* base, long long rows, long long cols
   cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
   cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1u, 1u};
+  // MN-major tf32: 128 B swizzle with 32 B atomicity (the only layout UMMA accepts for it)
+  static const int mn_swizzle = env_int("PDM_GEMM_MN_TMA_SWIZZLE", (int)CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+  const CUtensorMapSwizzle swz = mn_major ? (CUtensorMapSwizzle)mn_swizzle : CU_TENSOR_MAP_SWIZZLE_128B;
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   PDM_REQUIRE(r == CUDA_SUCCESS, PDM_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld cols=%lld ld=%lld box=%d)",
               (int)r, rows, cols, ld, box_rows);
@@ -336,11 +349,18 @@ extern "C" int pdm_gemm_tf32(const pdm_gemm_args* g, pdm_stream_t stream) {
   p.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
             ((uint32_t)(block_n >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
   p.tmem_cols = block_n <= 32 ? 32 : (block_n <= 64 ? 64 : (block_n <= 128 ? 128 : 256));
+  // MN-major descriptor fields (overridable for bring-up experiments)
+  static const int mn_layout = env_int("PDM_GEMM_MN_LAYOUT", 1);      // 1 = SWIZZLE_128B_BASE32B
+  static const int mn_sbo = env_int("PDM_GEMM_MN_SBO", 512);          // 4 k-rows x 128 B
+  static const int mn_lbo = env_int("PDM_GEMM_MN_LBO", (int)kAtomBytes);
+  p.mn_layout = (uint32_t)mn_layout;
+  p.mn_sbo = (uint32_t)mn_sbo;
+  p.mn_lbo = (uint32_t)mn_lbo;
 
   CUtensorMap ma, mb;
-  int rc = make_map(&ma, g->a, g->a_rows, g->a_cols, g->lda, p.a_mn ? kBlockK : kBlockM);
+  int rc = make_map(&ma, g->a, g->a_rows, g->a_cols, g->lda, p.a_mn ? kBlockK : kBlockM, p.a_mn);
   if (rc != PDM_OK) return rc;
-  rc = make_map(&mb, g->b, g->b_rows, g->b_cols, g->ldb, p.b_mn ? kBlockK : block_n);
+  rc = make_map(&mb, g->b, g->b_rows, g->b_cols, g->ldb, p.b_mn ? kBlockK : block_n, p.b_mn);
   if (rc != PDM_OK) return rc;
 
   const size_t smem = (size_t)kStages * (kABytes + (size_t)block_n * 128) + 256 + 1024;

@@ -38,6 +38,7 @@
 #include "common.cuh"
 
 #include <math.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -354,18 +355,36 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
   else __syncthreads();
 
   // ---- phase 2: reduce partials, all-reduce with peers, optimizer ----------
+  // 8 lanes share one float4 of the flat gradient: lane l sums partials l, l+8, ... (all loads
+  // in flight at once: one L2 round trip), then a fixed xor tree combines the 8 lanes, so the
+  // summation order depends only on G -- deterministic run to run.
   const int per_cta = (kFlat4 + G - 1) / G;
-  const int j_end = min(kFlat4, (cta + 1) * per_cta);
+  const int j_begin = cta * per_cta;
+  const int j_count = max(0, min(kFlat4, j_begin + per_cta) - j_begin);
   const int W = a.peers.world > 1 ? a.peers.world : 1;
   const uint32_t seq = a.peers.seq;
-  for (int j = cta * per_cta + tid; j < j_end; j += kThreads) {
+  const int sub = tid & 7;
+  for (int base = 0; base < j_count; base += kThreads / 8) {
+    const int jj = base + (tid >> 3);
+    const bool valid = jj < j_count;
+    const int j = j_begin + (valid ? jj : 0);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    const float* src = a.scratch + 4 * j;
-#pragma unroll 8
-    for (int c = 0; c < G; ++c) {
-      const float4 t4 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)c * kStride));
-      acc.x += t4.x; acc.y += t4.y; acc.z += t4.z; acc.w += t4.w;
+    if (valid) {
+      const float* src = a.scratch + 4 * j;
+#pragma unroll 4
+      for (int c = sub; c < G; c += 8) {
+        const float4 t4 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)c * kStride));
+        acc.x += t4.x; acc.y += t4.y; acc.z += t4.z; acc.w += t4.w;
+      }
     }
+#pragma unroll
+    for (int off = 1; off < 8; off <<= 1) {
+      acc.x += __shfl_xor_sync(0xffffffffu, acc.x, off);
+      acc.y += __shfl_xor_sync(0xffffffffu, acc.y, off);
+      acc.z += __shfl_xor_sync(0xffffffffu, acc.z, off);
+      acc.w += __shfl_xor_sync(0xffffffffu, acc.w, off);
+    }
+    if (!valid || sub != 0) continue;
     if (j == kFlat4 - 1) {
       // lanes z, w of the last float4 are this rank's {sum of losses, correct}
       if (a.step_out != nullptr) {
@@ -483,7 +502,10 @@ cudaError_t launch(const KernelArgs& ka, int x_dtype, int ctas, cudaStream_t str
   void* params[] = {&local};
   const void* fn = x_dtype == PDM_U8 ? (const void*)net_kernel<kRT, uint8_t, MODE>
                                      : (const void*)net_kernel<kRT, float, MODE>;
-  if (MODE == 0 && ctas > 1)
+  // PDM_NET_COOP=0 (measurement only) launches the barrier kernel without the co-residency
+  // guarantee; safe only while nothing else can occupy SMs of this GPU.
+  static const bool coop = [] { const char* e = getenv("PDM_NET_COOP"); return !(e && *e == '0'); }();
+  if (MODE == 0 && ctas > 1 && coop)
     return cudaLaunchCooperativeKernel(fn, dim3(ctas), dim3(kThreads), params, 0, stream);
   return cudaLaunchKernel(fn, dim3(ctas), dim3(kThreads), params, 0, stream);
 }

@@ -77,7 +77,7 @@ class DistributedDataParallel(nn.Module):
 
     def __init__(self, module, device_ids=None, output_device=None, broadcast_buffers=True,
                  bucket_cap_mb=DEFAULT_BUCKET_CAP_MB, comm='auto', fuse_optimizer=True,
-                 comm_timeout_s=30.0, process_group=None):
+                 comm_timeout_s=30.0, process_group=None, store=None):
         super().__init__()
         self.module = module
         params = [p for p in module.parameters() if p.requires_grad]
@@ -105,7 +105,7 @@ class DistributedDataParallel(nn.Module):
                 torch.cuda.set_device(self.device)
                 self.comm = PeerComm(self.rank, self.world, self.device,
                                      data_bytes=section * 4 * len(FlatState.SECTIONS) + 4096,
-                                     timeout_s=comm_timeout_s)
+                                     timeout_s=comm_timeout_s, store=store)
             elif comm == 'peer':
                 raise RuntimeError('--comm peer requested but the GPUs of this job cannot map each other\'s memory')
         self.uses_peer = self.comm is not None

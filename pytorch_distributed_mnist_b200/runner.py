@@ -85,9 +85,13 @@ def _run(args):
     model = build_model(getattr(args, 'arch', 'linear'), getattr(args, 'width', 1))
     if distributed_is_initialized():
         model.to(device)
+        store = None
+        if getattr(args, 'store', 'torch') == 'native' and device.type == 'cuda' and args.world_size > 1:
+            from .parallel.store import store_for_job
+            store = store_for_job(args.init_method, rank)
         model = DistributedDataParallel(
             model, device_ids=[device.index] if device.type == 'cuda' else None,
-            comm=getattr(args, 'comm', 'auto'))
+            comm=getattr(args, 'comm', 'auto'), store=store)
 
     optimizer = build_optimizer(getattr(args, 'optimizer', 'adam'), model.parameters(), args)
 
