@@ -67,6 +67,7 @@ struct KernelArgs {
   int y_dtype;
   int batch;
   int rows_per_cta;
+  int active;       // CTAs that own rows; the rest only help in phase 2
   float inv_batch;
   float* params;
   float* m;
@@ -188,7 +189,8 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
 #pragma unroll
     for (int i = 0; i < 4; ++i) { w[c][i] = 0.f; g[c][i] = 0.f; }
   }
-  if (owns_cols) {
+  const bool has_rows = MODE == 1 || cta < a.active;
+  if (owns_cols && has_rows) {
 #pragma unroll
     for (int c = 0; c < kOut; ++c) {
       const float4 t4 = *reinterpret_cast<const float4*>(a.params + c * kIn + 4 * tid);
@@ -336,7 +338,9 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
 
   // ---- publish this CTA's partial gradient ---------------------------------
   float* mine = a.scratch + (size_t)cta * kStride;
-  if (owns_cols) {
+  if (!has_rows) {
+    // helper CTA: nothing to publish
+  } else if (owns_cols) {
 #pragma unroll
     for (int c = 0; c < kOut; ++c)
       __stcg(reinterpret_cast<float4*>(mine + c * kIn + 4 * tid), make_float4(g[c][0], g[c][1], g[c][2], g[c][3]));
@@ -372,7 +376,7 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
     if (valid) {
       const float* src = a.scratch + 4 * j;
 #pragma unroll 4
-      for (int c = sub; c < G; c += 8) {
+      for (int c = sub; c < a.active; c += 8) {
         const float4 t4 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)c * kStride));
         acc.x += t4.x; acc.y += t4.y; acc.z += t4.z; acc.w += t4.w;
       }
@@ -484,15 +488,22 @@ OptConsts make_consts(const pdm_hyper& h, int world) {
   return oc;
 }
 
-void plan_rows(int batch, int want_ctas, int* ctas, int* rows_per_cta) {
+// ctas = CTAs launched; active = those that own a slice of the batch (ceil(batch / rows_per_cta)).
+// Small batches still launch kMinCtas CTAs: the extra ones skip phase 1 and shorten phase 2,
+// where the 1963 float4 of the gradient are divided among ALL launched CTAs.
+constexpr int kMinCtas = 64;
+void plan_rows(int batch, int want_ctas, int* ctas, int* active, int* rows_per_cta) {
   int g = want_ctas > 0 ? want_ctas : (batch + kRT - 1) / kRT;
+  if (want_ctas <= 0 && g < kMinCtas) g = kMinCtas;
   if (g > PDM_NET_MAX_CTAS) g = PDM_NET_MAX_CTAS;
   if (g < 1) g = 1;
   int rpc = (batch + g - 1) / g;
+  if (rpc < kRT && batch >= kRT) rpc = kRT;     // never split a tile's worth of rows further
   if (rpc < 1) rpc = 1;
-  g = (batch + rpc - 1) / rpc;
-  if (g < 1) g = 1;
+  int act = (batch + rpc - 1) / rpc;
+  if (act < 1) act = 1;
   *ctas = g;
+  *active = act;
   *rows_per_cta = rpc;
 }
 
@@ -513,8 +524,8 @@ cudaError_t launch(const KernelArgs& ka, int x_dtype, int ctas, cudaStream_t str
 }  // namespace
 
 extern "C" int pdm_net_default_ctas(int batch) {
-  int g, rpc;
-  plan_rows(batch, 0, &g, &rpc);
+  int g, act, rpc;
+  plan_rows(batch, 0, &g, &act, &rpc);
   return g;
 }
 
@@ -548,7 +559,7 @@ extern "C" int pdm_net_train_step(const pdm_net_step_args* args, pdm_stream_t st
   KernelArgs ka;
   memset(&ka, 0, sizeof(ka));
   int ctas = 0;
-  plan_rows(args->batch, args->ctas, &ctas, &ka.rows_per_cta);
+  plan_rows(args->batch, args->ctas, &ctas, &ka.active, &ka.rows_per_cta);
   ka.x = args->x;
   ka.y = args->y;
   ka.y_dtype = args->y_dtype;

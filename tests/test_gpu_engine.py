@@ -39,7 +39,7 @@ def test_engine_epoch_matches_torch_loop(opt, batch, workers):
     from pytorch_distributed_mnist_b200.ops.engine import NetEngine
     images, labels = _make(1000)
     net, fopt, ref, ropt = _build(opt=opt)
-    eng = NetEngine(fopt.flat, fopt, max_batch=batch, slots=4, workers=workers)
+    eng = NetEngine(fopt.flat, fopt, max_batch=256, slots=4, workers=workers)
     eng.set_dataset(images, labels)
     idx = torch.randperm(1000, generator=torch.Generator().manual_seed(1))
     steps, ms = eng.train(idx, batch)
