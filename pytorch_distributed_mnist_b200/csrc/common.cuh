@@ -65,7 +65,7 @@ __device__ __forceinline__ void grid_barrier(uint32_t* sync, uint32_t nblocks) {
       __threadfence();
       st_release_gpu(sync + 1, gen + 1);
     } else {
-      while (ld_acquire_gpu(sync + 1) == gen) { }   // pure spin: __nanosleep wakes on a ~4 us tick
+      while (ld_acquire_gpu(sync + 1) == gen) { }
     }
     __threadfence();
   }

@@ -78,6 +78,7 @@ struct KernelArgs {
   double* metrics;
   float* step_out;
   float* logits_out;
+  long long* trace;   // optional [gridDim.x][8] clock64 stamps (bring-up / profiling aid)
   OptConsts oc;
   pdm_peers peers;
 };
@@ -174,6 +175,8 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
   const int cta = blockIdx.x;
   const int G = gridDim.x;
   const bool owns_cols = tid < kCols4;
+#define PDM_TRACE(slot) do { if (MODE == 0 && a.trace != nullptr && tid == 0) a.trace[cta * 8 + (slot)] = clock64(); } while (0)
+  PDM_TRACE(0);
 
   // ---- one-time per CTA: LUT, bias, this thread's weight columns ----------
   if (sizeof(XT) == 1) {
@@ -211,6 +214,7 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
     if (owns_cols && row_begin + r < row_end) raw[r] = Raw::load(a.x, row_begin + r, tid);
   }
   __syncthreads();
+  PDM_TRACE(1);
 
   for (int row0 = row_begin; row0 < row_end; row0 += RT) {
     const int nrows = min(RT, row_end - row0);
@@ -355,8 +359,10 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
     __stcg(mine + PDM_NET_PARAMS + 1, k);
   }
 
+  PDM_TRACE(2);
   if (G > 1) grid_barrier(a.sync, (uint32_t)G);
   else __syncthreads();
+  PDM_TRACE(3);
 
   // ---- phase 2: reduce partials, all-reduce with peers, optimizer ----------
   // 8 lanes share one float4 of the flat gradient: lane l sums partials l, l+8, ... (all loads
@@ -460,6 +466,9 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
       if (a.v != nullptr) *reinterpret_cast<float4*>(a.v + 4 * j) = v4;
     }
   }
+  __syncthreads();
+  PDM_TRACE(4);
+#undef PDM_TRACE
 }
 
 // ---------------------------------------------------------------------------
@@ -507,9 +516,23 @@ void plan_rows(int batch, int want_ctas, int* ctas, int* active, int* rows_per_c
   *rows_per_cta = rpc;
 }
 
+// PDM_NET_TRACE=1: every training launch stamps clock64 at five points per CTA into a buffer
+// that pdm_net_trace_read copies out (used by benchmarks/step_trace.py; off by default).
+long long* g_trace_buf = nullptr;
+long long* trace_buffer() {
+  static const bool on = [] { const char* e = getenv("PDM_NET_TRACE"); return e && *e == '1'; }();
+  if (!on) return nullptr;
+  if (g_trace_buf == nullptr) {
+    if (cudaMalloc((void**)&g_trace_buf, PDM_NET_MAX_CTAS * 8 * sizeof(long long)) != cudaSuccess) return nullptr;
+    cudaMemset(g_trace_buf, 0, PDM_NET_MAX_CTAS * 8 * sizeof(long long));
+  }
+  return g_trace_buf;
+}
+
 template <int MODE>
 cudaError_t launch(const KernelArgs& ka, int x_dtype, int ctas, cudaStream_t stream) {
   KernelArgs local = ka;
+  if (MODE == 0) local.trace = trace_buffer();
   void* params[] = {&local};
   const void* fn = x_dtype == PDM_U8 ? (const void*)net_kernel<kRT, uint8_t, MODE>
                                      : (const void*)net_kernel<kRT, float, MODE>;
@@ -620,4 +643,14 @@ extern "C" int pdm_net_forward(const void* x, int x_dtype, int batch, const floa
   PDM_REQUIRE(logits != nullptr, PDM_ERR_ARG, "pdm_net_forward: logits is required");
   return eval_like(x, x_dtype, nullptr, PDM_U8, batch, params, logits, nullptr, (cudaStream_t)stream,
                    "pdm_net_forward");
+}
+
+// Copies the last training launch's per-CTA clock64 stamps ([PDM_NET_MAX_CTAS][8]) to `out`.
+// Only meaningful when the process runs with PDM_NET_TRACE=1; synchronises the device.
+extern "C" int pdm_net_trace_read(long long* out) {
+  PDM_REQUIRE(out != nullptr, PDM_ERR_ARG, "pdm_net_trace_read: out is NULL");
+  PDM_REQUIRE(g_trace_buf != nullptr, PDM_ERR_STATE, "pdm_net_trace_read: tracing is off (set PDM_NET_TRACE=1)");
+  PDM_CHECK_CUDA(cudaDeviceSynchronize());
+  PDM_CHECK_CUDA(cudaMemcpy(out, g_trace_buf, PDM_NET_MAX_CTAS * 8 * sizeof(long long), cudaMemcpyDeviceToHost));
+  return PDM_OK;
 }
