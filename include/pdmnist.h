@@ -123,6 +123,31 @@ int pdm_net_train_step(const pdm_net_step_args* args, pdm_stream_t stream);
 /* CTAs pdm_net_train_step will launch for a batch when args->ctas == 0. */
 int pdm_net_default_ctas(int batch);
 
+/* The same fused step for callers that must not allocate.  (This entry point has no
+ * counterpart in the reference, which ships no native code and never manages device memory.)
+ *
+ * Who needs it: a host that gave its whole device-memory budget to its own pool at start-up
+ * and forbids allocation afterwards (cudaMalloc/cudaFree also synchronise the device, which
+ * stalls other streams of a serving or real-time loop); code called from inside another
+ * allocator or under its lock; a recovery path after an out-of-memory error.  None of them can
+ * provide pdm_net_train_step's `scratch`/`sync`, so here those live in a fixed __device__ array
+ * inside the library: args->scratch and args->sync are ignored (may be NULL); x, y, params,
+ * m, v, grad_out, metrics, step_out are still the caller's.
+ *
+ * Limit: the array holds the partial gradients of at most PDM_NET_STATIC_MAX_CTAS CTAs
+ * (PDM_NET_STATIC_SCRATCH_BYTES, held by every GPU that loads the library until exit).
+ * args->ctas above that returns PDM_ERR_LIMIT; ctas == 0 picks the usual count clipped to the
+ * limit.  Every batch size works.
+ *
+ * First call on a device (with that device current) looks the array's device address up and
+ * caches it: make that call before any stream capture.  Nothing here allocates or frees.
+ * All calls on a device share the array and it keeps the previous call's contents; what must
+ * be zero is cleared in stream order on every call, but calls that overlap on one GPU race on
+ * the array -- serialise them. */
+#define PDM_NET_STATIC_MAX_CTAS 64
+#define PDM_NET_STATIC_SCRATCH_BYTES (PDM_NET_STATIC_MAX_CTAS * PDM_NET_SCRATCH_STRIDE * 4)
+int pdm_net_train_step_static(const pdm_net_step_args* args, pdm_stream_t stream);
+
 /* Forward + loss + top-1 only (ref:106-114).  metrics (4 doubles, device) is
  * accumulated atomically: += {loss*B, correct, B, 0}.  Any grid size; no scratch. */
 int pdm_net_eval_step(const void* x, int x_dtype, const void* y, int y_dtype, int batch,

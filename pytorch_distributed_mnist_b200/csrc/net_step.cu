@@ -38,6 +38,7 @@
 #include "common.cuh"
 
 #include <math.h>
+#include <pthread.h>
 #include <stdlib.h>
 
 namespace {
@@ -643,6 +644,155 @@ extern "C" int pdm_net_forward(const void* x, int x_dtype, int batch, const floa
   PDM_REQUIRE(logits != nullptr, PDM_ERR_ARG, "pdm_net_forward: logits is required");
   return eval_like(x, x_dtype, nullptr, PDM_U8, batch, params, logits, nullptr, (cudaStream_t)stream,
                    "pdm_net_forward");
+}
+
+// ---------------------------------------------------------------------------
+// pdm_net_train_step_static -- the same fused step for callers that must not allocate.
+//
+// pdm_net_train_step needs two pieces of device memory besides its inputs and outputs: the
+// per-CTA partial-gradient scratch and the two grid-barrier words.  Some hosts of this
+// library cannot supply them, because they cannot call cudaMalloc (or anything that does)
+// where the step runs:
+//   * a process that handed the whole HBM budget to its own pool at start-up and runs with a
+//     "no device allocation after init" rule (serving and real-time loops: cudaMalloc and
+//     cudaFree also synchronise the device, which stalls every other stream);
+//   * code called back from inside another framework's allocator or with that allocator's
+//     lock held, where re-entering an allocator deadlocks;
+//   * recovery paths that run after an out-of-memory error, when an allocation would fail again.
+// For them the scratch lives in this file as a fixed-size __device__ array that is part of the
+// loaded module: every GPU that loads the library holds PDM_NET_STATIC_SCRATCH_BYTES (about
+// 1.9 MiB) plus 256 bytes of barrier words until the process exits, whether or not this entry
+// point is ever called.  The size fixes the limit: at most PDM_NET_STATIC_MAX_CTAS (64) CTAs;
+// a larger request is refused with PDM_ERR_LIMIT.  Any batch size still works -- fewer CTAs
+// just take more rows each.
+//
+// Set-up: the first call on each device resolves the device addresses of the arrays with
+// cudaGetSymbolAddress (the array names are host-side handles in host code, not device
+// pointers) while that device is current, and caches them.  Make that first call outside any
+// stream capture.  No call here allocates or frees device or host memory.
+//
+// Sharing: all calls on a device use the same array, which keeps the last call's partial
+// gradients.  The step overwrites every element it later reads, and the barrier words -- the
+// only part that must start at zero -- are cleared in-stream before each launch, so stale
+// contents are harmless; but two calls that overlap on the same GPU (different streams,
+// different host threads) race on the array and must be serialised by the caller.
+// ---------------------------------------------------------------------------
+namespace {
+
+constexpr int kStaticMaxCtas = PDM_NET_STATIC_MAX_CTAS;
+constexpr int kStaticMaxDevices = 64;
+
+static __device__ __align__(256) float g_static_scratch[(size_t)kStaticMaxCtas * PDM_NET_SCRATCH_STRIDE];
+static __device__ __align__(256) uint32_t g_static_sync[64];
+
+static_assert(sizeof(float) * kStaticMaxCtas * PDM_NET_SCRATCH_STRIDE == PDM_NET_STATIC_SCRATCH_BYTES,
+              "PDM_NET_STATIC_SCRATCH_BYTES is out of date");
+
+struct StaticAddrs {
+  float* scratch = nullptr;
+  uint32_t* sync = nullptr;
+  bool ready = false;
+};
+StaticAddrs g_static_addrs[kStaticMaxDevices];
+pthread_mutex_t g_static_mu = PTHREAD_MUTEX_INITIALIZER;
+
+// Device addresses of the static arrays on the CURRENT device (resolved once per device).
+int static_addrs(StaticAddrs* out) {
+  int dev = -1;
+  PDM_CHECK_CUDA(cudaGetDevice(&dev));
+  PDM_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, PDM_ERR_LIMIT,
+              "pdm_net_train_step_static: device ordinal %d outside [0, %d)", dev, kStaticMaxDevices);
+  pthread_mutex_lock(&g_static_mu);
+  StaticAddrs cur = g_static_addrs[dev];
+  if (!cur.ready) {
+    void* ps = nullptr;
+    void* pb = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&ps, g_static_scratch);
+    if (e == cudaSuccess) e = cudaGetSymbolAddress(&pb, g_static_sync);
+    if (e != cudaSuccess || ps == nullptr || pb == nullptr) {
+      pthread_mutex_unlock(&g_static_mu);
+      pdm_set_error("pdm_net_train_step_static: cudaGetSymbolAddress on device %d -> %s", dev, cudaGetErrorString(e));
+      return PDM_ERR_CUDA;
+    }
+    cur.scratch = static_cast<float*>(ps);
+    cur.sync = static_cast<uint32_t*>(pb);
+    cur.ready = true;
+    g_static_addrs[dev] = cur;
+  }
+  pthread_mutex_unlock(&g_static_mu);
+  *out = cur;
+  return PDM_OK;
+}
+
+}  // namespace
+
+extern "C" int pdm_net_train_step_static(const pdm_net_step_args* args, pdm_stream_t stream) {
+  PDM_REQUIRE(args != nullptr, PDM_ERR_ARG, "pdm_net_train_step_static: args is NULL");
+  PDM_REQUIRE(args->batch >= 1, PDM_ERR_ARG, "pdm_net_train_step_static: batch must be >= 1 (got %d)", args->batch);
+  PDM_REQUIRE(args->x && args->y && args->params, PDM_ERR_ARG,
+              "pdm_net_train_step_static: x, y and params are required");
+  PDM_REQUIRE(args->x_dtype == PDM_U8 || args->x_dtype == PDM_F32, PDM_ERR_ARG,
+              "pdm_net_train_step_static: x_dtype must be PDM_U8 or PDM_F32");
+  PDM_REQUIRE(args->y_dtype == PDM_U8 || args->y_dtype == PDM_I64 || args->y_dtype == PDM_I32, PDM_ERR_ARG,
+              "pdm_net_train_step_static: y_dtype must be PDM_U8, PDM_I64 or PDM_I32");
+  PDM_REQUIRE(args->ctas >= 0, PDM_ERR_ARG, "pdm_net_train_step_static: ctas must be >= 0 (got %d)", args->ctas);
+  PDM_REQUIRE(args->ctas <= kStaticMaxCtas, PDM_ERR_LIMIT,
+              "pdm_net_train_step_static: %d CTAs requested but the built-in scratch holds at most %d "
+              "(PDM_NET_STATIC_MAX_CTAS); pass ctas <= %d, or use pdm_net_train_step with your own scratch",
+              args->ctas, kStaticMaxCtas, kStaticMaxCtas);
+  const pdm_hyper& h = args->hyper;
+  PDM_REQUIRE(h.opt == PDM_OPT_ADAM || h.opt == PDM_OPT_SGD || h.opt == PDM_OPT_NONE, PDM_ERR_ARG,
+              "pdm_net_train_step_static: unknown optimizer %d", h.opt);
+  PDM_REQUIRE(h.opt != PDM_OPT_ADAM || (args->m && args->v), PDM_ERR_ARG,
+              "pdm_net_train_step_static: Adam needs m and v");
+  PDM_REQUIRE(!(h.opt == PDM_OPT_SGD && h.beta1 != 0.f) || args->m, PDM_ERR_ARG,
+              "pdm_net_train_step_static: SGD with momentum needs m");
+  const int world = args->peers.world > 1 ? args->peers.world : 1;
+  PDM_REQUIRE(world <= PDM_MAX_RANKS, PDM_ERR_LIMIT, "pdm_net_train_step_static: world %d > %d", world, PDM_MAX_RANKS);
+  if (world > 1) {
+    PDM_REQUIRE(args->peers.seq != 0, PDM_ERR_ARG, "pdm_net_train_step_static: peers.seq must be non-zero");
+    PDM_REQUIRE(args->peers.rank >= 0 && args->peers.rank < world, PDM_ERR_ARG, "pdm_net_train_step_static: bad rank");
+    for (int p = 0; p < world; ++p)
+      PDM_REQUIRE(args->peers.inbox[p] != nullptr, PDM_ERR_STATE, "pdm_net_train_step_static: inbox[%d] not mapped", p);
+  }
+
+  StaticAddrs addrs;
+  int rc = static_addrs(&addrs);
+  if (rc != PDM_OK) return rc;
+
+  // CTA count: the caller's, or the usual choice for this batch clipped to what the array holds.
+  int want = args->ctas;
+  if (want == 0) {
+    want = pdm_net_default_ctas(args->batch);
+    if (want > kStaticMaxCtas) want = kStaticMaxCtas;
+  }
+  KernelArgs ka;
+  memset(&ka, 0, sizeof(ka));
+  int ctas = 0;
+  plan_rows(args->batch, want, &ctas, &ka.active, &ka.rows_per_cta);
+  PDM_REQUIRE(ctas >= 1 && ctas <= kStaticMaxCtas, PDM_ERR_LIMIT,
+              "pdm_net_train_step_static: planned %d CTAs, limit %d", ctas, kStaticMaxCtas);
+  ka.x = args->x;
+  ka.y = args->y;
+  ka.y_dtype = args->y_dtype;
+  ka.batch = args->batch;
+  ka.inv_batch = 1.0f / (float)args->batch;
+  ka.params = args->params;
+  ka.m = args->m;
+  ka.v = args->v;
+  ka.grad_out = args->grad_out;
+  ka.scratch = addrs.scratch;      // device address from cudaGetSymbolAddress, never the symbol itself
+  ka.sync = addrs.sync;
+  ka.metrics = args->metrics;
+  ka.step_out = args->step_out;
+  ka.oc = make_consts(h, world);
+  ka.peers = args->peers;
+  ka.peers.world = world;
+  // The barrier words are the only scratch that must start at zero (an aborted earlier launch
+  // could have left an arrival count behind): clear them in stream order.
+  PDM_CHECK_CUDA(cudaMemsetAsync(addrs.sync, 0, 2 * sizeof(uint32_t), (cudaStream_t)stream));
+  PDM_CHECK_CUDA(launch<0>(ka, args->x_dtype, ctas, (cudaStream_t)stream));
+  return PDM_OK;
 }
 
 // Copies the last training launch's per-CTA clock64 stamps ([PDM_NET_MAX_CTAS][8]) to `out`.

@@ -32,6 +32,7 @@ PDM_MAX_RANKS = 8
 NET_IN, NET_OUT, NET_PARAMS, NET_FLAT = 784, 10, 7850, 7852
 NET_SCRATCH_STRIDE = 7856
 NET_MAX_CTAS = 148
+NET_STATIC_MAX_CTAS = 64
 
 
 class Hyper(ctypes.Structure):
@@ -66,6 +67,8 @@ def _declare(lib):
     lib.pdm_device_ok.argtypes = [c_int]
     lib.pdm_net_train_step.argtypes = [ctypes.POINTER(NetStepArgs), c_void_p]
     lib.pdm_net_default_ctas.argtypes = [c_int]
+    if hasattr(lib, 'pdm_net_train_step_static'):
+        lib.pdm_net_train_step_static.argtypes = [ctypes.POINTER(NetStepArgs), c_void_p]
     lib.pdm_net_eval_step.argtypes = [c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]
     lib.pdm_net_forward.argtypes = [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]
     lib.pdm_optim_step.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
