@@ -184,6 +184,29 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
     // Bit-exact torchvision ToTensor (/255) + Normalize ((x-mean)/std), ref:132-135.
     sm.lut[tid] = __fdiv_rn(__fdiv_rn((float)tid, 255.0f) - kMean, kStd);
   }
+  const bool has_rows = MODE == 1 || cta < a.active;
+  float db = 0.f;          // threads 196..205: bias gradient of class tid-196
+  float my_loss = 0.f;     // softmax threads with c == 0
+  float my_correct = 0.f;
+
+  const int row_begin = cta * a.rows_per_cta;
+  const int row_end = min(a.batch, row_begin + a.rows_per_cta);
+
+  // The inputs do not depend on the previous step: start streaming them before waiting for it.
+  typename Raw::type raw[RT];
+#pragma unroll
+  for (int r = 0; r < RT; ++r) {
+    raw[r] = typename Raw::type();
+    if (owns_cols && row_begin + r < row_end) raw[r] = Raw::load(a.x, row_begin + r, tid);
+  }
+
+  // Programmatic dependent launch: everything above overlaps the tail of the previous step's
+  // kernel; parameters, optimizer state, scratch and barrier words are only touched below.
+  // (A no-op when the kernel was not launched with the PDL attribute.)
+  if (MODE == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
+
+  uint32_t bar_base = 0;
+  if (MODE == 0 && tid == 0 && G > 1) bar_base = ld_acquire_gpu(a.sync + 1);   // latency hidden by phase 1
   if (tid < 12) sm.bias[tid] = tid < kOut ? a.params[kIn * kOut + tid] : 0.f;
 
   float w[kOut][4];
@@ -193,26 +216,12 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
 #pragma unroll
     for (int i = 0; i < 4; ++i) { w[c][i] = 0.f; g[c][i] = 0.f; }
   }
-  const bool has_rows = MODE == 1 || cta < a.active;
   if (owns_cols && has_rows) {
 #pragma unroll
     for (int c = 0; c < kOut; ++c) {
       const float4 t4 = *reinterpret_cast<const float4*>(a.params + c * kIn + 4 * tid);
       w[c][0] = t4.x; w[c][1] = t4.y; w[c][2] = t4.z; w[c][3] = t4.w;
     }
-  }
-  float db = 0.f;          // threads 196..205: bias gradient of class tid-196
-  float my_loss = 0.f;     // softmax threads with c == 0
-  float my_correct = 0.f;
-
-  const int row_begin = cta * a.rows_per_cta;
-  const int row_end = min(a.batch, row_begin + a.rows_per_cta);
-
-  typename Raw::type raw[RT];
-#pragma unroll
-  for (int r = 0; r < RT; ++r) {
-    raw[r] = typename Raw::type();
-    if (owns_cols && row_begin + r < row_end) raw[r] = Raw::load(a.x, row_begin + r, tid);
   }
   __syncthreads();
   PDM_TRACE(1);
@@ -361,20 +370,48 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
   }
 
   PDM_TRACE(2);
-  if (G > 1) grid_barrier(a.sync, (uint32_t)G);
-  else __syncthreads();
-  PDM_TRACE(3);
-
-  // ---- phase 2: reduce partials, all-reduce with peers, optimizer ----------
-  // 8 lanes share one float4 of the flat gradient: lane l sums partials l, l+8, ... (all loads
-  // in flight at once: one L2 round trip), then a fixed xor tree combines the 8 lanes, so the
-  // summation order depends only on G -- deterministic run to run.
+  // ---- phase 2 set-up that does not need the barrier: which float4 this lane group owns, and
+  //      its parameter / optimizer-state loads (written last by the previous launch) ----------
   const int per_cta = (kFlat4 + G - 1) / G;
   const int j_begin = cta * per_cta;
   const int j_count = max(0, min(kFlat4, j_begin + per_cta) - j_begin);
   const int W = a.peers.world > 1 ? a.peers.world : 1;
   const uint32_t seq = a.peers.seq;
   const int sub = tid & 7;
+  const bool has_opt = a.oc.opt != PDM_OPT_NONE;
+  float4 p4_pre = make_float4(0.f, 0.f, 0.f, 0.f), m4_pre = p4_pre, v4_pre = p4_pre;
+  if (has_opt && sub == 0 && (tid >> 3) < j_count) {
+    const int j = j_begin + (tid >> 3);
+    p4_pre = *reinterpret_cast<const float4*>(a.params + 4 * j);
+    if (a.m != nullptr) m4_pre = *reinterpret_cast<const float4*>(a.m + 4 * j);
+    if (a.v != nullptr) v4_pre = *reinterpret_cast<const float4*>(a.v + 4 * j);
+  }
+
+  // ---- grid barrier: sync[0] counts arrivals (never reset), sync[1] holds the count at which
+  //      this launch started.  Arrival is a fire-and-forget red; only the polls are round trips.
+  if (G > 1) {
+    __syncthreads();
+    if (tid == 0) {
+      __threadfence();
+      asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(a.sync) : "memory");
+      const uint32_t target = bar_base + (uint32_t)G;
+      while ((int32_t)(ld_acquire_gpu(a.sync) - target) < 0) { }
+      if (cta == 0) a.sync[1] = target;          // base of the next launch on these words
+      __threadfence();
+    }
+    __syncthreads();
+  } else {
+    __syncthreads();
+  }
+  // Let the next step's kernel start its input prefetch (PDL); it still waits for this grid to
+  // finish before it touches parameters or scratch.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  PDM_TRACE(3);
+
+  // ---- phase 2: reduce partials, all-reduce with peers, optimizer ----------
+  // 8 lanes share one float4 of the flat gradient: lane l sums partials l, l+8, ... (loads all in
+  // flight: one L2 round trip), then a fixed xor tree combines the 8 lanes, so the summation order
+  // depends only on the CTA count -- deterministic run to run.
   for (int base = 0; base < j_count; base += kThreads / 8) {
     const int jj = base + (tid >> 3);
     const bool valid = jj < j_count;
@@ -382,10 +419,16 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (valid) {
       const float* src = a.scratch + 4 * j;
-#pragma unroll 4
-      for (int c = sub; c < a.active; c += 8) {
-        const float4 t4 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)c * kStride));
-        acc.x += t4.x; acc.y += t4.y; acc.z += t4.z; acc.w += t4.w;
+      for (int c0 = sub; c0 < a.active; c0 += 64) {
+        float4 t[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int c = c0 + 8 * u;
+          t[u] = c < a.active ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)c * kStride))
+                              : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { acc.x += t[u].x; acc.y += t[u].y; acc.z += t[u].z; acc.w += t[u].w; }
       }
     }
 #pragma unroll
@@ -451,11 +494,13 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
     acc.x *= iw; acc.y *= iw; acc.z *= iw; acc.w *= iw;
     if (a.grad_out != nullptr) *reinterpret_cast<float4*>(a.grad_out + 4 * j) = acc;
 
-    if (a.oc.opt != PDM_OPT_NONE) {
-      float4 p4 = *reinterpret_cast<float4*>(a.params + 4 * j);
-      float4 m4 = make_float4(0.f, 0.f, 0.f, 0.f), v4 = m4;
-      if (a.m != nullptr) m4 = *reinterpret_cast<float4*>(a.m + 4 * j);
-      if (a.v != nullptr) v4 = *reinterpret_cast<float4*>(a.v + 4 * j);
+    if (has_opt) {
+      float4 p4 = p4_pre, m4 = m4_pre, v4 = v4_pre;
+      if (base != 0) {          // only the first pass was prefetched before the barrier
+        p4 = *reinterpret_cast<float4*>(a.params + 4 * j);
+        if (a.m != nullptr) m4 = *reinterpret_cast<float4*>(a.m + 4 * j);
+        if (a.v != nullptr) v4 = *reinterpret_cast<float4*>(a.v + 4 * j);
+      }
       opt_update(a.oc, acc.x, p4.x, m4.x, v4.x);
       opt_update(a.oc, acc.y, p4.y, m4.y, v4.y);
       if (j != kFlat4 - 1) {  // the last two floats are padding, not parameters
@@ -475,7 +520,33 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
 // ---------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------
-constexpr int kRT = 8;
+constexpr int kRT = 8;    // rows per tile of the evaluation kernel and default of the training kernel
+
+// Rows per tile of the training kernel: 8 (default) or 4 (PDM_NET_RT=4: twice the CTAs for the
+// same batch, half the phase-1 work per CTA).
+int train_rt() {
+  static const int rt = [] { const char* e = getenv("PDM_NET_RT"); return (e && *e == '4') ? 4 : 8; }();
+  return rt;
+}
+// How the training kernel is launched (PDM_NET_LAUNCH):
+//   coop  (default) cooperative launch: co-residency of all CTAs is guaranteed by the driver
+//   pdl   programmatic dependent launch: the next step's input prefetch overlaps this step's tail.
+//         Not cooperative; safe here because the grid never exceeds one CTA per SM, the only kernels
+//         it can overlap are its own predecessor (independent of it) and its successor (released
+//         only after this grid's barrier, i.e. once every CTA is resident)
+//   plain ordinary launch (measurement only)
+enum { LAUNCH_COOP = 0, LAUNCH_PDL = 1, LAUNCH_PLAIN = 2 };
+int launch_mode() {
+  static const int mode = [] {
+    const char* e = getenv("PDM_NET_LAUNCH");
+    if (e && !strcmp(e, "pdl")) return (int)LAUNCH_PDL;
+    if (e && !strcmp(e, "plain")) return (int)LAUNCH_PLAIN;
+    const char* c = getenv("PDM_NET_COOP");
+    if (c && *c == '0') return (int)LAUNCH_PLAIN;
+    return (int)LAUNCH_COOP;
+  }();
+  return mode;
+}
 
 OptConsts make_consts(const pdm_hyper& h, int world) {
   OptConsts oc;
@@ -503,12 +574,13 @@ OptConsts make_consts(const pdm_hyper& h, int world) {
 // where the 1963 float4 of the gradient are divided among ALL launched CTAs.
 constexpr int kMinCtas = 64;
 void plan_rows(int batch, int want_ctas, int* ctas, int* active, int* rows_per_cta) {
-  int g = want_ctas > 0 ? want_ctas : (batch + kRT - 1) / kRT;
+  const int rt = train_rt();
+  int g = want_ctas > 0 ? want_ctas : (batch + rt - 1) / rt;
   if (want_ctas <= 0 && g < kMinCtas) g = kMinCtas;
   if (g > PDM_NET_MAX_CTAS) g = PDM_NET_MAX_CTAS;
   if (g < 1) g = 1;
   int rpc = (batch + g - 1) / g;
-  if (rpc < kRT && batch >= kRT) rpc = kRT;     // never split a tile's worth of rows further
+  if (rpc < rt && batch >= rt) rpc = rt;        // never split a tile's worth of rows further
   if (rpc < 1) rpc = 1;
   int act = (batch + rpc - 1) / rpc;
   if (act < 1) act = 1;
@@ -535,12 +607,28 @@ cudaError_t launch(const KernelArgs& ka, int x_dtype, int ctas, cudaStream_t str
   KernelArgs local = ka;
   if (MODE == 0) local.trace = trace_buffer();
   void* params[] = {&local};
-  const void* fn = x_dtype == PDM_U8 ? (const void*)net_kernel<kRT, uint8_t, MODE>
-                                     : (const void*)net_kernel<kRT, float, MODE>;
-  // PDM_NET_COOP=0 (measurement only) launches the barrier kernel without the co-residency
-  // guarantee; safe only while nothing else can occupy SMs of this GPU.
-  static const bool coop = [] { const char* e = getenv("PDM_NET_COOP"); return !(e && *e == '0'); }();
-  if (MODE == 0 && ctas > 1 && coop)
+  const void* fn;
+  if (MODE == 0 && train_rt() == 4)
+    fn = x_dtype == PDM_U8 ? (const void*)net_kernel<4, uint8_t, MODE> : (const void*)net_kernel<4, float, MODE>;
+  else
+    fn = x_dtype == PDM_U8 ? (const void*)net_kernel<kRT, uint8_t, MODE> : (const void*)net_kernel<kRT, float, MODE>;
+  if (MODE != 0) return cudaLaunchKernel(fn, dim3(ctas), dim3(kThreads), params, 0, stream);
+  const int mode = launch_mode();
+  if (mode == LAUNCH_PDL) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(ctas);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelExC(&cfg, fn, params);
+  }
+  if (mode == LAUNCH_COOP && ctas > 1)
     return cudaLaunchCooperativeKernel(fn, dim3(ctas), dim3(kThreads), params, 0, stream);
   return cudaLaunchKernel(fn, dim3(ctas), dim3(kThreads), params, 0, stream);
 }
