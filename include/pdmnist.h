@@ -103,7 +103,9 @@ typedef struct pdm_peers {
  *  metrics  optional 4 doubles, device: += {loss*B, correct, B, 0}
  *  step_out optional 2 floats, device or mapped host: {mean loss, #correct}
  *  ctas     0 = choose from B; else 1..PDM_NET_MAX_CTAS
- * The kernel is launched cooperatively; all its CTAs must fit on the GPU. */
+ * All CTAs of the launch must fit on the GPU at once (they meet at a grid barrier): the launch is
+ * a programmatic-dependent one when the grid fits one CTA per SM, else (or with
+ * PDM_NET_LAUNCH=coop) a cooperative one, which the driver refuses if it cannot be co-resident. */
 typedef struct pdm_net_step_args {
   const void* x; int32_t x_dtype;
   const void* y; int32_t y_dtype;

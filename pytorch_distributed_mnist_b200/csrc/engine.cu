@@ -11,9 +11,11 @@
 //   * the two host syncs per step (ref:94-95, K12/K13): the per-step
 //     {loss, correct} pair is copied back asynchronously and only read after
 //     the epoch's last step.
-// Steps alternate between two streams so the H2D copy of step n+1 overlaps
-// the kernel of step n; kernel n+1 waits on kernel n through an event (the
-// parameters are a true dependency).  Five CUDA calls per step on the host.
+// Two streams: a copy stream that runs ahead issuing the H2D copies (throttled only by
+// "slot consumed" events, `slots` steps back) and a compute stream that runs the step
+// kernels back to back, each waiting on its slot's "copy done" event.  The kernel writes
+// its {loss, correct} pair straight into mapped pinned host memory (an 8-byte device->host
+// store per step), so there is no D2H memcpy in the loop.  Six CUDA calls per step.
 #include "common.cuh"
 
 #include <atomic>
@@ -47,6 +49,22 @@ bool debug_on() {
   if (v < 0) { const char* e = getenv("PDM_ENGINE_DEBUG"); v = (e && *e && *e != '0') ? 1 : 0; }
   return v == 1;
 }
+// PDM_ENGINE_PROFILE=1: host time spent per section of the step loop, printed after each run.
+bool profile_on() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("PDM_ENGINE_PROFILE"); v = (e && *e && *e != '0') ? 1 : 0; }
+  return v == 1;
+}
+struct HostProf {
+  double t[6] = {0, 0, 0, 0, 0, 0};   // wait-filled, h2d+events, launch, record+d2h, sync-old, total
+  std::chrono::steady_clock::time_point last;
+  void start() { last = std::chrono::steady_clock::now(); }
+  void lap(int i) {
+    const auto now = std::chrono::steady_clock::now();
+    t[i] += std::chrono::duration<double, std::micro>(now - last).count();
+    last = now;
+  }
+};
 #define DBG(...) do { if (debug_on()) { fprintf(stderr, "[pdm_engine] " __VA_ARGS__); fputc('\n', stderr); fflush(stderr); } } while (0)
 
 }  // namespace
@@ -68,11 +86,12 @@ struct pdm_engine {
   float* step_out = nullptr;              // [slots][2]
   std::vector<uint8_t*> dev_slot;         // [slots] packed batch
   std::vector<uint8_t*> host_slot;        // [slots] pinned staging
-  float* host_results = nullptr;          // pinned [capacity][2]
+  float* host_results = nullptr;          // pinned + mapped [capacity][2]
+  float* host_results_dev = nullptr;      // device alias of host_results
   int64_t host_results_cap = 0;
-  cudaStream_t stream[2] = {nullptr, nullptr};
-  std::vector<cudaEvent_t> h2d_done;      // per slot
-  cudaEvent_t kernel_done[2] = {nullptr, nullptr};
+  cudaStream_t stream[2] = {nullptr, nullptr};   // [0] compute, [1] copy
+  std::vector<cudaEvent_t> h2d_done;      // per slot, recorded on the copy stream
+  std::vector<cudaEvent_t> consumed;      // per slot, recorded on the compute stream after its kernel
   cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
   // dataset (host, not owned)
   const uint8_t* images = nullptr;
@@ -152,7 +171,8 @@ int ensure_results(pdm_engine* e, int64_t nsteps) {
   e->host_results = nullptr;
   e->host_results_cap = 0;
   const int64_t cap = std::max<int64_t>(nsteps, 1024);
-  PDM_CHECK_CUDA(cudaHostAlloc((void**)&e->host_results, (size_t)cap * 2 * sizeof(float), cudaHostAllocDefault));
+  PDM_CHECK_CUDA(cudaHostAlloc((void**)&e->host_results, (size_t)cap * 2 * sizeof(float), cudaHostAllocMapped));
+  PDM_CHECK_CUDA(cudaHostGetDevicePointer((void**)&e->host_results_dev, e->host_results, 0));
   e->host_results_cap = cap;
   return PDM_OK;
 }
@@ -198,14 +218,15 @@ int pdm_engine_create(pdm_engine** out, int device, int max_batch, int slots, in
   e->dev_slot.assign(slots, nullptr);
   e->host_slot.assign(slots, nullptr);
   e->h2d_done.assign(slots, nullptr);
+  e->consumed.assign(slots, nullptr);
   for (int s = 0; s < slots; ++s) {
     ENGINE_TRY(cudaMalloc((void**)&e->dev_slot[s], slot_bytes));
     ENGINE_TRY(cudaHostAlloc((void**)&e->host_slot[s], slot_bytes, cudaHostAllocDefault));
     ENGINE_TRY(cudaEventCreateWithFlags(&e->h2d_done[s], cudaEventDisableTiming));
+    ENGINE_TRY(cudaEventCreateWithFlags(&e->consumed[s], cudaEventDisableTiming));
   }
   for (int i = 0; i < 2; ++i) {
     ENGINE_TRY(cudaStreamCreateWithFlags(&e->stream[i], cudaStreamNonBlocking));
-    ENGINE_TRY(cudaEventCreateWithFlags(&e->kernel_done[i], cudaEventDisableTiming));
   }
   ENGINE_TRY(cudaEventCreate(&e->ev_begin));
   ENGINE_TRY(cudaEventCreate(&e->ev_end));
@@ -280,25 +301,36 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
   pdm_hyper h;
   if (hyper) h = *hyper;
   else memset(&h, 0, sizeof(h));
+  const bool prof = profile_on();
+  HostProf hp;
+  const auto t_loop0 = std::chrono::steady_clock::now();
+  cudaStream_t cs = e->stream[0];   // compute
+  cudaStream_t xs = e->stream[1];   // copy
   for (int64_t b = 0; b < nsteps && rc == PDM_OK; ++b) {
+    if (prof) hp.start();
     const int s = (int)(b % e->slots);
-    cudaStream_t st = e->stream[b & 1];
     const int64_t lo = b * batch;
     const int n = (int)std::min<int64_t>(batch, count - lo);
     {
       std::unique_lock<std::mutex> lk(e->mu);
       e->cv_filled.wait(lk, [&] { return e->filled_batch[s] == b; });
     }
+    if (prof) hp.lap(0);
     DBG("main issues step %lld (slot %d, n=%d)", (long long)b, s, n);
+    // ---- copy stream: device slot s is free once the kernel of step b - slots has run ----
     const size_t bytes = (size_t)n * kSample;
-    cudaError_t ce = cudaMemcpyAsync(e->dev_slot[s], e->host_slot[s], bytes, cudaMemcpyHostToDevice, st);
-    if (ce == cudaSuccess) ce = cudaEventRecord(e->h2d_done[s], st);
-    if (ce == cudaSuccess && b > 0) ce = cudaStreamWaitEvent(st, e->kernel_done[(b - 1) & 1], 0);
+    cudaError_t ce = cudaSuccess;
+    if (b >= e->slots) ce = cudaStreamWaitEvent(xs, e->consumed[s], 0);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(e->dev_slot[s], e->host_slot[s], bytes, cudaMemcpyHostToDevice, xs);
+    if (ce == cudaSuccess) ce = cudaEventRecord(e->h2d_done[s], xs);
+    // ---- compute stream: kernels run back to back, each after its slot's copy ----
+    if (ce == cudaSuccess) ce = cudaStreamWaitEvent(cs, e->h2d_done[s], 0);
     if (ce != cudaSuccess) {
       pdm_set_error("pdm_engine_run: step %lld copy/record -> %s", (long long)b, cudaGetErrorString(ce));
       rc = PDM_ERR_CUDA;
       break;
     }
+    if (prof) hp.lap(1);
     if (train) {
       pdm_net_step_args a;
       memset(&a, 0, sizeof(a));
@@ -314,31 +346,29 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
       a.scratch = e->scratch;
       a.sync = e->sync;
       a.metrics = e->metrics;
-      a.step_out = e->step_out + 2 * s;
+      a.step_out = e->host_results_dev + 2 * b;     // mapped host memory: the step's D2H transfer
       a.hyper = h;
       a.hyper.step = h.step + b;
       if (e->comm != nullptr) {
         rc = pdm_comm_peers(e->comm, &a.peers, 1);
         if (rc != PDM_OK) break;
       }
-      rc = pdm_net_train_step(&a, st);
-      if (rc != PDM_OK) break;
-      ce = cudaEventRecord(e->kernel_done[b & 1], st);
-      if (ce == cudaSuccess)
-        ce = cudaMemcpyAsync(e->host_results + 2 * b, e->step_out + 2 * s, 2 * sizeof(float), cudaMemcpyDeviceToHost, st);
+      rc = pdm_net_train_step(&a, cs);
     } else {
       rc = pdm_net_eval_step(e->dev_slot[s], PDM_U8, e->dev_slot[s] + (size_t)n * kImg, PDM_U8, n, e->params, nullptr,
-                             e->metrics, st);
-      if (rc != PDM_OK) break;
-      ce = cudaEventRecord(e->kernel_done[b & 1], st);
+                             e->metrics, cs);
     }
+    if (rc != PDM_OK) break;
+    if (prof) hp.lap(2);
+    ce = cudaEventRecord(e->consumed[s], cs);
     if (ce != cudaSuccess) {
-      pdm_set_error("pdm_engine_run: step %lld record/readback -> %s", (long long)b, cudaGetErrorString(ce));
+      pdm_set_error("pdm_engine_run: step %lld record -> %s", (long long)b, cudaGetErrorString(ce));
       rc = PDM_ERR_CUDA;
       break;
     }
-    // The staging slot may be refilled once its H2D copy has completed.  Check the slot
-    // used slots/2 steps ago so the wait is normally already satisfied.
+    // The pinned staging slot may be refilled once its H2D copy has completed.  Look at the
+    // slot used slots/2 steps ago so the wait is normally already satisfied.
+    if (prof) hp.lap(3);
     const int64_t old = b - e->slots / 2;
     if (old >= 0) {
       const int so = (int)(old % e->slots);
@@ -354,6 +384,7 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
       }
       e->cv_free.notify_all();
     }
+    if (prof) hp.lap(4);
   }
   if (rc != PDM_OK) {
     // release the workers before reporting the failure
@@ -364,8 +395,13 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
     }
     e->cv_free.notify_all();
   }
+  if (prof) {
+    const double tot = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_loop0).count();
+    fprintf(stderr, "[pdm_engine] host us/step over %lld steps: wait-staged %.2f | h2d+events %.2f | launch %.2f | "
+            "record %.2f | slot-sync %.2f | loop total %.2f\n", (long long)nsteps, hp.t[0] / nsteps, hp.t[1] / nsteps,
+            hp.t[2] / nsteps, hp.t[3] / nsteps, hp.t[4] / nsteps, tot / nsteps);
+  }
   DBG("all steps issued, draining streams");
-  cudaStreamWaitEvent(e->stream[0], e->kernel_done[1], 0);
   cudaStreamSynchronize(e->stream[1]);
   cudaEventRecord(e->ev_end, e->stream[0]);
   cudaError_t se = cudaStreamSynchronize(e->stream[0]);
@@ -465,8 +501,8 @@ int pdm_engine_destroy(pdm_engine* e) {
   for (auto p : e->dev_slot) if (p) cudaFree(p);
   for (auto p : e->host_slot) if (p) cudaFreeHost(p);
   for (auto ev : e->h2d_done) if (ev) cudaEventDestroy(ev);
+  for (auto ev : e->consumed) if (ev) cudaEventDestroy(ev);
   for (int i = 0; i < 2; ++i) {
-    if (e->kernel_done[i]) cudaEventDestroy(e->kernel_done[i]);
     if (e->stream[i]) cudaStreamDestroy(e->stream[i]);
   }
   if (e->ev_begin) cudaEventDestroy(e->ev_begin);
