@@ -89,7 +89,7 @@ struct pdm_engine {
   float* host_results = nullptr;          // pinned + mapped [capacity][2]
   float* host_results_dev = nullptr;      // device alias of host_results
   int64_t host_results_cap = 0;
-  cudaStream_t stream[2] = {nullptr, nullptr};   // [0] compute, [1] copy
+  cudaStream_t stream[3] = {nullptr, nullptr, nullptr};   // [0] compute, [1], [2] copy (alternating)
   std::vector<cudaEvent_t> h2d_done;      // per slot, recorded on the copy stream
   std::vector<cudaEvent_t> consumed;      // per slot, recorded on the compute stream after its kernel
   cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
@@ -118,10 +118,16 @@ void gather_batch(pdm_engine* e, const Job& job, int64_t b, uint8_t* dst) {
   uint8_t* img = dst;
   uint8_t* lab = dst + (size_t)n * kImg;
   const int64_t* idx = job.indices + lo;
+  constexpr int kAhead = 8;   // rows: a shuffled gather is DRAM-latency bound without prefetch
   int64_t i = 0;
   while (i < n) {  // coalesce runs of consecutive indices into one memcpy
     int64_t j = i + 1;
     while (j < n && idx[j] == idx[j - 1] + 1) ++j;
+    if (j == i + 1 && i + kAhead < n) {
+      const uint8_t* nxt = e->images + (size_t)idx[i + kAhead] * kImg;
+      for (int off = 0; off < kImg; off += 64) __builtin_prefetch(nxt + off, 0, 0);
+      __builtin_prefetch(e->labels + idx[i + kAhead], 0, 0);
+    }
     memcpy(img + (size_t)i * kImg, e->images + (size_t)idx[i] * kImg, (size_t)(j - i) * kImg);
     memcpy(lab + i, e->labels + idx[i], (size_t)(j - i));
     i = j;
@@ -225,7 +231,7 @@ int pdm_engine_create(pdm_engine** out, int device, int max_batch, int slots, in
     ENGINE_TRY(cudaEventCreateWithFlags(&e->h2d_done[s], cudaEventDisableTiming));
     ENGINE_TRY(cudaEventCreateWithFlags(&e->consumed[s], cudaEventDisableTiming));
   }
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < 3; ++i) {
     ENGINE_TRY(cudaStreamCreateWithFlags(&e->stream[i], cudaStreamNonBlocking));
   }
   ENGINE_TRY(cudaEventCreate(&e->ev_begin));
@@ -296,6 +302,7 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
   // both streams start after everything already queued on the device
   PDM_CHECK_CUDA(cudaEventRecord(e->ev_begin, e->stream[0]));
   PDM_CHECK_CUDA(cudaStreamWaitEvent(e->stream[1], e->ev_begin, 0));
+  PDM_CHECK_CUDA(cudaStreamWaitEvent(e->stream[2], e->ev_begin, 0));
 
   int rc = PDM_OK;
   pdm_hyper h;
@@ -305,7 +312,6 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
   HostProf hp;
   const auto t_loop0 = std::chrono::steady_clock::now();
   cudaStream_t cs = e->stream[0];   // compute
-  cudaStream_t xs = e->stream[1];   // copy
   for (int64_t b = 0; b < nsteps && rc == PDM_OK; ++b) {
     if (prof) hp.start();
     const int s = (int)(b % e->slots);
@@ -320,7 +326,10 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
     // ---- copy stream: device slot s is free once the kernel of step b - slots has run ----
     const size_t bytes = (size_t)n * kSample;
     cudaError_t ce = cudaSuccess;
-    if (b >= e->slots) ce = cudaStreamWaitEvent(xs, e->consumed[s], 0);
+    // two copy streams take turns so one stream's event bookkeeping overlaps the other's DMA
+    cudaStream_t xs = e->stream[1 + (b & 1)];
+    // the stream-side wait is only needed when the consuming kernel is not known to be done
+    if (b >= e->slots && cudaEventQuery(e->consumed[s]) != cudaSuccess) ce = cudaStreamWaitEvent(xs, e->consumed[s], 0);
     if (ce == cudaSuccess) ce = cudaMemcpyAsync(e->dev_slot[s], e->host_slot[s], bytes, cudaMemcpyHostToDevice, xs);
     if (ce == cudaSuccess) ce = cudaEventRecord(e->h2d_done[s], xs);
     // ---- compute stream: kernels run back to back, each after its slot's copy ----
@@ -403,6 +412,7 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
   }
   DBG("all steps issued, draining streams");
   cudaStreamSynchronize(e->stream[1]);
+  cudaStreamSynchronize(e->stream[2]);
   cudaEventRecord(e->ev_end, e->stream[0]);
   cudaError_t se = cudaStreamSynchronize(e->stream[0]);
   {
@@ -502,7 +512,7 @@ int pdm_engine_destroy(pdm_engine* e) {
   for (auto p : e->host_slot) if (p) cudaFreeHost(p);
   for (auto ev : e->h2d_done) if (ev) cudaEventDestroy(ev);
   for (auto ev : e->consumed) if (ev) cudaEventDestroy(ev);
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < 3; ++i) {
     if (e->stream[i]) cudaStreamDestroy(e->stream[i]);
   }
   if (e->ev_begin) cudaEventDestroy(e->ev_begin);
