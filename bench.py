@@ -164,8 +164,10 @@ def run_ours(opts):
     # loaders of exactly W and K steps per rank (the distributed sampler shards N x steps x B samples)
     warm_loader = pdm.MNISTDataLoader('unused', B, num_workers=opts.workers, train=True, synthetic=True,
                                       size=max(1, W) * B * world)
+    # the timed pass walks the standard 60,000-sample set (the reference's working set, 47 MB) for
+    # exactly K steps per rank: successive epoch permutations, sharded by the distributed sampler
     timed_loader = pdm.MNISTDataLoader('unused', B, num_workers=opts.workers, train=True, synthetic=True,
-                                       size=K * B * world, seed=4321)
+                                       seed=4321, samples_per_epoch=K * B)
     trainer = pdm.Trainer(model, optimizer, warm_loader, warm_loader, device, fused='on', ctas=opts.ctas,
                           loader_workers=opts.workers)
     engine = trainer.engine

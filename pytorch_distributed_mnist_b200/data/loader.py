@@ -87,7 +87,7 @@ class ShardSampler(object):
 class MNISTDataLoader(object):
 
     def __init__(self, root, batch_size, num_workers=0, train=True,
-                 synthetic=None, seed=1234, size=None):
+                 synthetic=None, seed=1234, size=None, samples_per_epoch=None):
         if batch_size < 1:
             raise ValueError('per-process batch size must be >= 1 (got {}); '
                              '--batch-size is the node total and is divided by the GPU count'
@@ -100,6 +100,9 @@ class MNISTDataLoader(object):
         self.train = train
         self.batch_size = batch_size
         self.num_workers = num_workers
+        # Optional fixed pass length (per process): a pass then walks as many successive epoch
+        # permutations as needed.  Fixed-length "virtual epochs" for schedules and benchmarks.
+        self.samples_per_epoch = samples_per_epoch
 
         self.sampler = None
         if train and distributed_is_initialized():
@@ -119,19 +122,38 @@ class MNISTDataLoader(object):
         return self
 
     def num_samples(self):
+        if self.samples_per_epoch is not None:
+            return int(self.samples_per_epoch)
         return len(self.sampler) if self.sampler is not None else len(self.labels)
 
     def __len__(self):
         return math.ceil(self.num_samples() / self.batch_size)
 
     # -- index plan ---------------------------------------------------------
-    def epoch_indices(self):
-        """The sample order for one pass, as an int64 tensor."""
+    def _one_epoch(self, epoch_offset=0):
         if self.sampler is not None:
+            if epoch_offset:
+                base = self.sampler.epoch
+                self.sampler.set_epoch(base + epoch_offset)
+                idx = self.sampler.indices()
+                self.sampler.set_epoch(base)
+                return idx
             return self.sampler.indices()
         if self.shuffle:
             return torch.randperm(len(self.labels))
         return torch.arange(len(self.labels))
+
+    def epoch_indices(self):
+        """The sample order for one pass, as an int64 tensor."""
+        if self.samples_per_epoch is None:
+            return self._one_epoch()
+        want, parts, have, k = int(self.samples_per_epoch), [], 0, 0
+        while have < want:
+            part = self._one_epoch(k)
+            parts.append(part)
+            have += part.numel()
+            k += 1
+        return torch.cat(parts)[:want].contiguous()
 
     # -- iteration ----------------------------------------------------------
     def raw_batches(self):
