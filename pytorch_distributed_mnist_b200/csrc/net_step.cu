@@ -463,30 +463,40 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
         ll_store2(dst, acc.x, acc.y, seq);
         ll_store2(dst + 2, acc.z, acc.w, seq);
       }
-      float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+      // Poll every peer's slot in the same pass (loads to all of them in flight together), keep a
+      // bit per peer still missing, then add in rank order so every rank computes the same sum.
       const uint64_t* inbox = a.peers.inbox[a.peers.rank];
+      float4 q[PDM_MAX_RANKS];
+      uint32_t pending = ((1u << W) - 1u) & ~(1u << a.peers.rank);   // bit p: peer p's slot not complete yet
+      uint32_t half_ok = 0;                                          // bits [2p, 2p+1]: halves already valid
       uint64_t t0 = 0;
-      for (int p = 0; p < W; ++p) {
-        float4 q = acc;
-        if (p != a.peers.rank) {
-          const uint64_t* s = inbox + ((par + p) * kFlat4 + j) * 4;
-          uint32_t spins = 0;
-          bool ok0 = false, ok1 = false;
-          while (true) {
-            if (!ok0) ok0 = ll_load2(s, seq, q.x, q.y);
-            if (!ok1) ok1 = ll_load2(s + 2, seq, q.z, q.w);
-            if (ok0 && ok1) break;
-            if ((++spins & 1023u) == 0u && a.peers.timeout_ns != 0) {
-              const uint64_t now = globaltimer_ns();
-              if (t0 == 0) t0 = now;
-              else if (now - t0 > a.peers.timeout_ns) {
-                if (a.peers.status != nullptr) atomicExch(a.peers.status, 1 + p);
-                break;
-              }
-            }
+      uint32_t spins = 0;
+      while (pending != 0u) {
+#pragma unroll
+        for (int p = 0; p < PDM_MAX_RANKS; ++p) {
+          if (p < W && (pending >> p) & 1u) {
+            const uint64_t* s = inbox + ((par + p) * kFlat4 + j) * 4;
+            if (!((half_ok >> (2 * p)) & 1u) && ll_load2(s, seq, q[p].x, q[p].y)) half_ok |= 1u << (2 * p);
+            if (!((half_ok >> (2 * p + 1)) & 1u) && ll_load2(s + 2, seq, q[p].z, q[p].w)) half_ok |= 2u << (2 * p);
+            if (((half_ok >> (2 * p)) & 3u) == 3u) pending &= ~(1u << p);
           }
         }
-        sum.x += q.x; sum.y += q.y; sum.z += q.z; sum.w += q.w;
+        if (pending != 0u && (++spins & 1023u) == 0u && a.peers.timeout_ns != 0) {
+          const uint64_t now = globaltimer_ns();
+          if (t0 == 0) t0 = now;
+          else if (now - t0 > a.peers.timeout_ns) {
+            if (a.peers.status != nullptr) atomicExch(a.peers.status, 1 + __ffs(pending) - 1);
+            break;
+          }
+        }
+      }
+      float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int p = 0; p < PDM_MAX_RANKS; ++p) {
+        if (p < W) {
+          const float4 t4 = p == a.peers.rank ? acc : q[p];
+          sum.x += t4.x; sum.y += t4.y; sum.z += t4.z; sum.w += t4.w;
+        }
       }
       acc = sum;
     }

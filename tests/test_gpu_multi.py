@@ -188,8 +188,8 @@ def test_bucketed_fused_allreduce_optimizer_cnn(free_port):
 def _run_worker(rank, world, port, out_dir):
     from pytorch_distributed_mnist_b200.cli import build_parser
     from pytorch_distributed_mnist_b200 import runner
-    args = build_parser().parse_args(['--world-size', str(world), '--synthetic', '--train-size', '8192', '--test-size',
-                                      '2048', '--batch-size', str(64 * world), '--epochs', '2', '-i',
+    args = build_parser().parse_args(['--world-size', str(world), '--synthetic', '--train-size', str(4096 * world),
+                                      '--test-size', '2048', '--batch-size', str(64 * world), '--epochs', '2', '-i',
                                       'tcp://127.0.0.1:{}'.format(port), '--checkpoint-dir', out_dir])
     args.rank = rank
     out = runner.run(args)
