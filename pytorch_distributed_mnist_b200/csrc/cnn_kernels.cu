@@ -82,34 +82,81 @@ __global__ void __launch_bounds__(256) conv1_fwd_kernel(const XT* __restrict__ x
 }
 
 // ------------------------------------------------------------------ conv1 backward (wgrad + bias grad)
-// dz [B*676, c1] (already ReLU-masked).  One warp walks pixels; lane owns channels lane, lane+32, ...
+// dw[c][k] += sum_q dz[q][c] * x[q + tap k],  db[c] += sum_q dz[q][c]   (dz already ReLU-masked).
+// One CTA walks a contiguous range of pixels in chunks of 64: the 9 input taps of every pixel are
+// computed once into smem, then each warp takes 8 pixels and lane = channel (mod 32) accumulates
+// its 10 sums in registers for every channel group.  One block-level reduction and c1*10 atomics
+// per CTA at the end; dz is read exactly once, coalesced.
+constexpr int kC1Chunk = 64;        // pixels per chunk
+constexpr int kC1MaxGroups = 8;     // channel groups of 32 held in registers (c1 <= 256)
+
 template <typename XT>
 __global__ void __launch_bounds__(256) conv1_bwd_kernel(const XT* __restrict__ x, const float* __restrict__ dz,
-                                                        float* __restrict__ dw, float* __restrict__ db, int batch, int c1) {
-  const int lane = threadIdx.x & 31;
-  const int warps_total = gridDim.x * (blockDim.x >> 5);
-  const int gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+                                                        float* __restrict__ dw, float* __restrict__ db, int batch, int c1,
+                                                        int pixels_per_cta) {
+  __shared__ float patch[kC1Chunk][9];
+  __shared__ float red[8][32 * 10];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long pixels = (long long)batch * 676;
-  for (int c0 = 0; c0 < c1; c0 += 32) {
-    const int c = c0 + lane;
-    float acc[10];
+  const long long p_begin = (long long)blockIdx.x * pixels_per_cta;
+  const long long p_end = min(pixels, p_begin + pixels_per_cta);
+  const int groups = (c1 + 31) / 32;
+  float acc[kC1MaxGroups][10];
 #pragma unroll
-    for (int k = 0; k < 10; ++k) acc[k] = 0.f;
-    for (long long pix = gw; pix < pixels; pix += warps_total) {
-      const int n = (int)(pix / 676), r = (int)(pix % 676), h = r / 26, wv = r % 26;
-      const float g = c < c1 ? dz[pix * c1 + c] : 0.f;
+  for (int g = 0; g < kC1MaxGroups; ++g)
 #pragma unroll
-      for (int k = 0; k < 9; ++k) {
+    for (int k = 0; k < 10; ++k) acc[g][k] = 0.f;
+
+  for (long long c0 = p_begin; c0 < p_end; c0 += kC1Chunk) {
+    const int n_here = (int)min((long long)kC1Chunk, p_end - c0);
+    __syncthreads();
+    for (int t = threadIdx.x; t < kC1Chunk * 9; t += blockDim.x) {
+      const int pi = t / 9, k = t % 9;
+      float v = 0.f;
+      if (pi < n_here) {
+        const long long pix = c0 + pi;
+        const int n = (int)(pix / 676), r = (int)(pix % 676), h = r / 26, wv = r % 26;
         const XT raw = x[(size_t)n * 784 + (h + k / 3) * 28 + (wv + k % 3)];
-        const float xv = sizeof(XT) == 1 ? __fdiv_rn(__fdiv_rn((float)raw, 255.0f) - kMean, kStd) : (float)raw;
-        acc[k] = fmaf(g, xv, acc[k]);
+        v = sizeof(XT) == 1 ? __fdiv_rn(__fdiv_rn((float)raw, 255.0f) - kMean, kStd) : (float)raw;
       }
-      acc[9] += g;
+      patch[pi][k] = v;
     }
-    if (c < c1) {
+    __syncthreads();
+    for (int pi = warp; pi < n_here; pi += 8) {
+      float xv[9];
 #pragma unroll
-      for (int k = 0; k < 9; ++k) atomicAdd(dw + c * 9 + k, acc[k]);
-      atomicAdd(db + c, acc[9]);
+      for (int k = 0; k < 9; ++k) xv[k] = patch[pi][k];
+      const float* row = dz + (c0 + pi) * c1;
+#pragma unroll
+      for (int g = 0; g < kC1MaxGroups; ++g) {
+        if (g < groups) {
+          const int c = g * 32 + lane;
+          const float d = c < c1 ? __ldg(row + c) : 0.f;
+#pragma unroll
+          for (int k = 0; k < 9; ++k) acc[g][k] = fmaf(d, xv[k], acc[g][k]);
+          acc[g][9] += d;
+        }
+      }
+    }
+  }
+  // block reduction, one channel group at a time
+#pragma unroll
+  for (int g = 0; g < kC1MaxGroups; ++g) {
+    if (g < groups) {
+      __syncthreads();
+#pragma unroll
+      for (int k = 0; k < 10; ++k) red[warp][lane * 10 + k] = acc[g][k];
+      __syncthreads();
+      for (int t = threadIdx.x; t < 320; t += blockDim.x) {
+        float sum = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) sum += red[w][t];
+        const int c = g * 32 + t / 10, k = t % 10;
+        if (c < c1) {
+          if (k < 9) atomicAdd(dw + c * 9 + k, sum);
+          else atomicAdd(db + c, sum);
+        }
+      }
     }
   }
 }
@@ -324,11 +371,15 @@ int pdm_conv1_fwd(const void* x, int x_dtype, const float* w, const float* bias,
 
 int pdm_conv1_bwd(const void* x, int x_dtype, const float* dz, float* dw, float* db, int batch, int c1, pdm_stream_t stream) {
   PDM_REQUIRE(x && dz && dw && db && batch >= 1 && c1 >= 1, PDM_ERR_ARG, "pdm_conv1_bwd: bad arguments");
-  const int grid = grid_for((long long)batch * 676, 8 * 64, 148 * 4);
+  PDM_REQUIRE(c1 <= 32 * kC1MaxGroups, PDM_ERR_LIMIT, "pdm_conv1_bwd: at most %d channels (got %d)", 32 * kC1MaxGroups, c1);
+  const long long pixels = (long long)batch * 676;
+  int per_cta = 512;
+  while ((pixels + per_cta - 1) / per_cta > 148 * 8) per_cta *= 2;
+  const int grid = (int)((pixels + per_cta - 1) / per_cta);
   if (x_dtype == PDM_U8)
-    conv1_bwd_kernel<uint8_t><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint8_t*)x, dz, dw, db, batch, c1);
+    conv1_bwd_kernel<uint8_t><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint8_t*)x, dz, dw, db, batch, c1, per_cta);
   else
-    conv1_bwd_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, dz, dw, db, batch, c1);
+    conv1_bwd_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, dz, dw, db, batch, c1, per_cta);
   PDM_CHECK_CUDA(cudaGetLastError());
   return PDM_OK;
 }

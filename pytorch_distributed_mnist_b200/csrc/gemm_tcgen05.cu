@@ -6,7 +6,9 @@
 //
 //   D[M,N] (+)= A[M,K] . B[N,K]^T        tf32 x tf32 -> fp32
 //
-// One CTA per 128 x BLOCK_N output tile (optionally per K split), 192 threads:
+// Persistent: one CTA per SM walks 128 x BLOCK_N output tiles (optionally K splits); the fp32
+// accumulator is double-buffered in TMEM so the epilogue of tile i overlaps the MMAs of tile i+1.
+// 192 threads:
 //   warp 0      TMA producer   cp.async.bulk.tensor.2d -> 128B-swizzled smem ring (4 stages),
 //                              completion by mbarrier complete_tx
 //   warp 1      MMA issuer     one lane issues tcgen05.mma.cta_group::1.kind::tf32 (M=128,
@@ -53,8 +55,9 @@ struct Params {
   int M, N;
   int block_n;
   int a_mn, b_mn;            // 1 = MN-major operand
-  int kblocks_per_split;     // k-blocks each CTA walks
+  int kblocks_per_split;     // k-blocks per (tile, split)
   int kblocks_total;
+  int tiles_m, tiles_n, splits;
   int mode, img_w, cblocks, shift_sign;
   float* D;
   long long ldd;
@@ -138,6 +141,13 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
 
 __device__ __forceinline__ int tap_shift(int tap, int img_w) { return (tap / 3) * img_w + (tap % 3); }
 
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// Persistent kernel: CTA c walks tiles c, c + gridDim.x, ... (n fastest, then m, then K split).
+// The accumulator is double-buffered in TMEM (2 x BLOCK_N columns): while the epilogue warps
+// drain tile i, the MMA warp already accumulates tile i+1, and the TMA ring never stops.
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const __grid_constant__ Params p) {
@@ -148,20 +158,18 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   const uint32_t stage_bytes = kABytes + b_bytes;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * stage_bytes);
   uint64_t* empty = full + kStages;
-  uint64_t* tmem_full = empty + kStages;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint64_t* tmem_full = empty + kStages;       // [2]
+  uint64_t* tmem_empty = tmem_full + 2;        // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * kBlockM;
-  const int n0 = blockIdx.y * p.block_n;
-  const int kb_begin = blockIdx.z * p.kblocks_per_split;
-  int nkb = p.kblocks_total - kb_begin;
-  if (nkb > p.kblocks_per_split) nkb = p.kblocks_per_split;
+  const int tiles_mn = p.tiles_m * p.tiles_n;
+  const int tiles_total = tiles_mn * p.splits;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
-    mbar_init(tmem_full, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(tmem_full + s, 1); mbar_init(tmem_empty + s, 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
@@ -176,87 +184,121 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     // =============================== TMA producer ===============================
     if (lane == 0) {
       const uint32_t tx = kABytes + b_bytes;
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % kStages;
-        const uint32_t ph = (uint32_t)(i / kStages) & 1u;
-        mbar_wait(empty + s, ph ^ 1u);
-        uint8_t* sa = smem + s * stage_bytes;
-        uint8_t* sb = sa + kABytes;
-        mbar_expect_tx(full + s, tx);
-        const int kb = kb_begin + i;
-        // ---- A ----
-        if (p.mode == MODE_CONV) {
-          const int tap = kb / p.cblocks, cb = kb % p.cblocks;
-          tma_load_2d(sa, &map_a, full + s, cb * kBlockK, m0 + p.shift_sign * tap_shift(tap, p.img_w));
-        } else if (!p.a_mn) {
-          tma_load_2d(sa, &map_a, full + s, kb * kBlockK, m0);
-        } else {
-          for (int a = 0; a < kBlockM / kAtom; ++a)
-            tma_load_2d(sa + a * kAtomBytes, &map_a, full + s, m0 + a * kAtom, kb * kBlockK);
-        }
-        // ---- B ----
-        if (p.mode == MODE_WGRAD) {
-          for (int j = 0; j < p.block_n / kAtom; ++j) {
-            const int n = n0 + j * kAtom;
-            const int tap = n / (p.cblocks * kAtom), cb = (n / kAtom) % p.cblocks;
-            tma_load_2d(sb + j * kAtomBytes, &map_b, full + s, cb * kAtom, kb * kBlockK + tap_shift(tap, p.img_w));
+      uint32_t it = 0;                                  // k-blocks issued so far (ring position)
+      for (int t = blockIdx.x; t < tiles_total; t += gridDim.x) {
+        const int z = t / tiles_mn, rem = t % tiles_mn;
+        const int m0 = (rem / p.tiles_n) * kBlockM, n0 = (rem % p.tiles_n) * p.block_n;
+        const int kb_begin = z * p.kblocks_per_split;
+        const int nkb = min(p.kblocks_per_split, p.kblocks_total - kb_begin);
+        for (int i = 0; i < nkb; ++i, ++it) {
+          const int s = it % kStages;
+          const uint32_t ph = (it / kStages) & 1u;
+          mbar_wait(empty + s, ph ^ 1u);
+          uint8_t* sa = smem + s * stage_bytes;
+          uint8_t* sb = sa + kABytes;
+          mbar_expect_tx(full + s, tx);
+          const int kb = kb_begin + i;
+          // ---- A ----
+          if (p.mode == MODE_CONV) {
+            const int tap = kb / p.cblocks, cb = kb % p.cblocks;
+            tma_load_2d(sa, &map_a, full + s, cb * kBlockK, m0 + p.shift_sign * tap_shift(tap, p.img_w));
+          } else if (!p.a_mn) {
+            tma_load_2d(sa, &map_a, full + s, kb * kBlockK, m0);
+          } else {
+            for (int a = 0; a < kBlockM / kAtom; ++a)
+              tma_load_2d(sa + a * kAtomBytes, &map_a, full + s, m0 + a * kAtom, kb * kBlockK);
           }
-        } else if (!p.b_mn) {
-          tma_load_2d(sb, &map_b, full + s, kb * kBlockK, n0);
-        } else {
-          for (int j = 0; j < p.block_n / kAtom; ++j)
-            tma_load_2d(sb + j * kAtomBytes, &map_b, full + s, n0 + j * kAtom, kb * kBlockK);
+          // ---- B ----
+          if (p.mode == MODE_WGRAD) {
+            for (int j = 0; j < p.block_n / kAtom; ++j) {
+              const int n = n0 + j * kAtom;
+              const int tap = n / (p.cblocks * kAtom), cb = (n / kAtom) % p.cblocks;
+              tma_load_2d(sb + j * kAtomBytes, &map_b, full + s, cb * kAtom, kb * kBlockK + tap_shift(tap, p.img_w));
+            }
+          } else if (!p.b_mn) {
+            tma_load_2d(sb, &map_b, full + s, kb * kBlockK, n0);
+          } else {
+            for (int j = 0; j < p.block_n / kAtom; ++j)
+              tma_load_2d(sb + j * kAtomBytes, &map_b, full + s, n0 + j * kAtom, kb * kBlockK);
+          }
         }
       }
     }
   } else if (warp == 1) {
     // =============================== MMA issuer =================================
     if (lane == 0) {
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % kStages;
-        const uint32_t ph = (uint32_t)(i / kStages) & 1u;
-        mbar_wait(full + s, ph);
+      uint32_t it = 0, tl = 0;
+      for (int t = blockIdx.x; t < tiles_total; t += gridDim.x, ++tl) {
+        const int z = t / tiles_mn;
+        const int kb_begin = z * p.kblocks_per_split;
+        const int nkb = min(p.kblocks_per_split, p.kblocks_total - kb_begin);
+        const uint32_t as = tl & 1u, aph = (tl >> 1) & 1u;
+        mbar_wait(tmem_empty + as, aph ^ 1u);           // epilogue has drained this accumulator
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + s * stage_bytes);
-        const uint32_t sb = sa + kABytes;
+        const uint32_t tmem_d = tmem_base + as * (uint32_t)p.block_n;
+        for (int i = 0; i < nkb; ++i, ++it) {
+          const int s = it % kStages;
+          const uint32_t ph = (it / kStages) & 1u;
+          mbar_wait(full + s, ph);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * stage_bytes);
+          const uint32_t sb = sa + kABytes;
 #pragma unroll
-        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-          // K-major: next 8 k = +32 bytes inside the swizzle atom.  MN-major: next 8 k-rows = +1024 bytes.
-          const uint64_t da = p.a_mn ? make_desc(sa + k * 1024, p.mn_lbo, p.mn_sbo, p.mn_layout) : make_desc(sa + k * 32, 0, 1024);
-          const uint64_t db = p.b_mn ? make_desc(sb + k * 1024, p.mn_lbo, p.mn_sbo, p.mn_layout) : make_desc(sb + k * 32, 0, 1024);
-          umma_tf32(tmem_base, da, db, p.idesc, (i | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            // K-major: next 8 k = +32 bytes inside the swizzle atom.  MN-major: next 8 k-rows = +1024 bytes.
+            const uint64_t da = p.a_mn ? make_desc(sa + k * 1024, p.mn_lbo, p.mn_sbo, p.mn_layout) : make_desc(sa + k * 32, 0, 1024);
+            const uint64_t db = p.b_mn ? make_desc(sb + k * 1024, p.mn_lbo, p.mn_sbo, p.mn_layout) : make_desc(sb + k * 32, 0, 1024);
+            umma_tf32(tmem_d, da, db, p.idesc, (i | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(empty + s);        // stage reusable once these MMAs have read it
         }
-        umma_commit(empty + s);        // stage reusable once these MMAs have read it
+        umma_commit(tmem_full + as);     // accumulator complete
       }
-      umma_commit(tmem_full);          // accumulator complete
     }
   } else {
     // =============================== epilogue ====================================
-    mbar_wait(tmem_full, 0);
-    tc_fence_after();
-    const int quad = warp & 3;                         // TMEM lane quadrant this warp may read
-    const int row = m0 + quad * 32 + lane;
-    const bool row_ok = row < p.M && nkb > 0;
-    float* drow = p.D + (long long)row * p.ldd;
-    const float* mrow = p.mask ? p.mask + (long long)row * p.ld_mask : nullptr;
-    for (int c = 0; c < p.block_n; c += 16) {
-      float v[16];
-      tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c, v);
-      if (!row_ok) continue;
-      const int col0 = n0 + c;
+    const int quad = warp & 3;                           // TMEM lane quadrant this warp may read
+    uint32_t tl = 0;
+    for (int t = blockIdx.x; t < tiles_total; t += gridDim.x, ++tl) {
+      const int rem = t % tiles_mn;
+      const int m0 = (rem / p.tiles_n) * kBlockM, n0 = (rem % p.tiles_n) * p.block_n;
+      const uint32_t as = tl & 1u, aph = (tl >> 1) & 1u;
+      mbar_wait(tmem_full + as, aph);
+      tc_fence_after();
+      const int row = m0 + quad * 32 + lane;
+      const bool row_ok = row < p.M;
+      float* drow = p.D + (long long)row * p.ldd;
+      const float* mrow = p.mask ? p.mask + (long long)row * p.ld_mask : nullptr;
+      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + as * (uint32_t)p.block_n;
+      for (int c = 0; c < p.block_n; c += 16) {
+        float v[16];
+        tmem_ld16(taddr + (uint32_t)c, v);
+        if (!row_ok) continue;
+        const int col0 = n0 + c;
+        if (col0 >= p.N) continue;
+        if (!p.atomic && !p.bias && !mrow && !p.relu && col0 + 16 <= p.N &&
+            (reinterpret_cast<uintptr_t>(drow + col0) & 15) == 0) {
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int col = col0 + i;
-        if (col >= p.N) break;
-        float x = v[i];
-        if (p.bias) x += __ldg(p.bias + col);
-        if (p.relu) x = fmaxf(x, 0.f);
-        if (mrow) x = __ldg(mrow + col) > 0.f ? x : 0.f;
-        if (p.atomic) atomicAdd(drow + col, x);
-        else drow[col] = x;
+          for (int i = 0; i < 16; i += 4)
+            *reinterpret_cast<float4*>(drow + col0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+          continue;
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int col = col0 + i;
+          if (col >= p.N) break;
+          float x = v[i];
+          if (p.bias) x += __ldg(p.bias + col);
+          if (p.relu) x = fmaxf(x, 0.f);
+          if (mrow) x = __ldg(mrow + col) > 0.f ? x : 0.f;
+          if (p.atomic) atomicAdd(drow + col, x);
+          else drow[col] = x;
+        }
       }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tmem_empty + as);       // 4 epilogue warps release the accumulator
     }
-    tc_fence_before();
   }
   __syncthreads();
   if (warp == 1) {
@@ -348,7 +390,11 @@ extern "C" int pdm_gemm_tf32(const pdm_gemm_args* g, pdm_stream_t stream) {
   // instruction descriptor: D=f32 (bits 4-5 = 1), A,B = tf32 (bits 7-9, 10-12 = 2), majors (15, 16), N>>3 (17-22), M>>4 (24-28)
   p.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
             ((uint32_t)(block_n >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
-  p.tmem_cols = block_n <= 32 ? 32 : (block_n <= 64 ? 64 : (block_n <= 128 ? 128 : 256));
+  const int acc_cols = 2 * block_n;        // double-buffered accumulator
+  p.tmem_cols = acc_cols <= 32 ? 32 : (acc_cols <= 64 ? 64 : (acc_cols <= 128 ? 128 : (acc_cols <= 256 ? 256 : 512)));
+  p.tiles_m = (g->M + kBlockM - 1) / kBlockM;
+  p.tiles_n = (g->N + block_n - 1) / block_n;
+  p.splits = splits;
   // MN-major descriptor fields (overridable for bring-up experiments)
   static const int mn_layout = env_int("PDM_GEMM_MN_LAYOUT", 1);      // 1 = SWIZZLE_128B_BASE32B
   static const int mn_sbo = env_int("PDM_GEMM_MN_SBO", 512);          // 4 k-rows x 128 B
@@ -363,13 +409,24 @@ extern "C" int pdm_gemm_tf32(const pdm_gemm_args* g, pdm_stream_t stream) {
   rc = make_map(&mb, g->b, g->b_rows, g->b_cols, g->ldb, p.b_mn ? kBlockK : block_n, p.b_mn);
   if (rc != PDM_OK) return rc;
 
-  const size_t smem = (size_t)kStages * (kABytes + (size_t)block_n * 128) + 256 + 1024;
+  // at least half of the SM's shared memory so that two CTAs never share an SM (and its TMEM)
+  size_t smem = (size_t)kStages * (kABytes + (size_t)block_n * 128) + 256 + 1024;
+  if (smem < 120 * 1024) smem = 120 * 1024;
   static bool attr_set = false;
   if (!attr_set) {
     PDM_CHECK_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
-  dim3 grid((g->M + kBlockM - 1) / kBlockM, (g->N + block_n - 1) / block_n, splits);
+  static int sm_count = 0;
+  if (sm_count == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
+    if (sm_count <= 0) sm_count = 148;
+  }
+  // one persistent CTA per SM (TMEM and the smem ring are sized for one resident CTA)
+  const long long tiles_total = (long long)p.tiles_m * p.tiles_n * splits;
+  const int grid = (int)(tiles_total < sm_count ? tiles_total : sm_count);
   gemm_tf32_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(ma, mb, p);
   PDM_CHECK_CUDA(cudaGetLastError());
   return PDM_OK;
