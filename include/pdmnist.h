@@ -119,6 +119,9 @@ typedef struct pdm_net_step_args {
   float* step_out;
   pdm_hyper hyper;
   pdm_peers peers;
+  const int32_t* row_index;   /* optional, device: batch row r is row row_index[r] of x and y.  Lets the
+                                 kernel gather a shuffled batch itself from a dataset that is resident in
+                                 device memory -- or in pinned, mapped host memory (zero-copy over PCIe). */
 } pdm_net_step_args;
 
 int pdm_net_train_step(const pdm_net_step_args* args, pdm_stream_t stream);
@@ -309,6 +312,13 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
 int pdm_engine_run_device(pdm_engine* e, const uint8_t* dev_images, const uint8_t* dev_labels,
                           int64_t pool_samples, int batch, int64_t nsteps, const pdm_hyper* hyper,
                           int ctas, float* device_ms);
+/* In-kernel gather path (B200-first: the dataset fits HBM many times over).  place: mode 0 copies
+ * the dataset to device memory once; mode 1 page-locks + maps the caller's host arrays so the step
+ * kernel reads its rows straight from host memory over PCIe (zero-copy).  run_gather uploads the
+ * index plan (4 B/sample) once, then issues one launch per step. */
+int pdm_engine_place_dataset(pdm_engine* e, const uint8_t* images, const uint8_t* labels, int64_t n, int mode);
+int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, int batch,
+                          const pdm_hyper* hyper, int ctas, float* step_results, float* device_ms);
 int pdm_engine_metrics(pdm_engine* e, double out[4], int reset);
 void* pdm_engine_scratch(pdm_engine* e);
 void* pdm_engine_sync_words(pdm_engine* e);

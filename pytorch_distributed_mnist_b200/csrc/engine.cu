@@ -99,6 +99,15 @@ struct pdm_engine {
   const uint8_t* images = nullptr;
   const uint8_t* labels = nullptr;
   int64_t n_samples = 0;
+  // dataset as the kernels see it on the in-kernel-gather path (pdm_engine_place_dataset)
+  int placed_mode = -1;                   // -1 none, 0 device copy (owned), 1 host arrays registered + mapped
+  uint8_t* placed_images = nullptr;       // device pointer (copy or alias)
+  uint8_t* placed_labels = nullptr;
+  void* registered_images = nullptr;      // host ranges to unregister
+  void* registered_labels = nullptr;
+  int64_t placed_n = 0;
+  int32_t* idx_dev = nullptr;             // index plan of the current pass
+  int64_t idx_cap = 0;
   // worker pool
   std::vector<std::thread> workers;
   std::mutex mu;
@@ -499,6 +508,123 @@ int pdm_engine_run_device(pdm_engine* e, const uint8_t* dev_images, const uint8_
   return PDM_OK;
 }
 
+static void unplace_dataset(pdm_engine* e) {
+  if (e->placed_mode == 0) {
+    if (e->placed_images) cudaFree(e->placed_images);
+    if (e->placed_labels) cudaFree(e->placed_labels);
+  } else if (e->placed_mode == 1) {
+    if (e->registered_images) cudaHostUnregister(e->registered_images);
+    if (e->registered_labels) cudaHostUnregister(e->registered_labels);
+  }
+  e->placed_mode = -1;
+  e->placed_images = e->placed_labels = nullptr;
+  e->registered_images = e->registered_labels = nullptr;
+  e->placed_n = 0;
+  cudaGetLastError();
+}
+
+// Make the dataset visible to the in-kernel gather (pdm_engine_run_gather).
+//   mode 0  copy it into device memory once (60,000 MNIST images are 47 MB of a 180 GB HBM)
+//   mode 1  page-lock and map the caller's host arrays; the step kernel then reads its rows
+//           straight out of host memory over PCIe (zero-copy) -- no staging copy, no H2D memcpy
+// The host arrays must stay alive (mode 1: and unmoved) until the engine is destroyed or re-placed.
+int pdm_engine_place_dataset(pdm_engine* e, const uint8_t* images, const uint8_t* labels, int64_t n, int mode) {
+  PDM_REQUIRE(e && images && labels && n >= 1, PDM_ERR_ARG, "pdm_engine_place_dataset: bad arguments");
+  PDM_REQUIRE(mode == 0 || mode == 1, PDM_ERR_ARG, "pdm_engine_place_dataset: mode must be 0 (device) or 1 (zero-copy)");
+  PDM_REQUIRE(n <= 0x7fffffffLL, PDM_ERR_LIMIT, "pdm_engine_place_dataset: at most 2^31-1 samples");
+  PDM_CHECK_CUDA(cudaSetDevice(e->device));
+  PDM_CHECK_CUDA(cudaDeviceSynchronize());
+  unplace_dataset(e);
+  if (mode == 0) {
+    PDM_CHECK_CUDA(cudaMalloc((void**)&e->placed_images, (size_t)n * kImg));
+    PDM_CHECK_CUDA(cudaMalloc((void**)&e->placed_labels, (size_t)n));
+    e->placed_mode = 0;
+    PDM_CHECK_CUDA(cudaMemcpy(e->placed_images, images, (size_t)n * kImg, cudaMemcpyHostToDevice));
+    PDM_CHECK_CUDA(cudaMemcpy(e->placed_labels, labels, (size_t)n, cudaMemcpyHostToDevice));
+  } else {
+    cudaError_t ce = cudaHostRegister(const_cast<uint8_t*>(images), (size_t)n * kImg, cudaHostRegisterMapped);
+    PDM_REQUIRE(ce == cudaSuccess, PDM_ERR_CUDA, "pdm_engine_place_dataset: cudaHostRegister(images) -> %s", cudaGetErrorString(ce));
+    e->registered_images = const_cast<uint8_t*>(images);
+    e->placed_mode = 1;
+    ce = cudaHostRegister(const_cast<uint8_t*>(labels), (size_t)n, cudaHostRegisterMapped);
+    PDM_REQUIRE(ce == cudaSuccess, PDM_ERR_CUDA, "pdm_engine_place_dataset: cudaHostRegister(labels) -> %s", cudaGetErrorString(ce));
+    e->registered_labels = const_cast<uint8_t*>(labels);
+    PDM_CHECK_CUDA(cudaHostGetDevicePointer((void**)&e->placed_images, e->registered_images, 0));
+    PDM_CHECK_CUDA(cudaHostGetDevicePointer((void**)&e->placed_labels, e->registered_labels, 0));
+  }
+  e->placed_n = n;
+  return PDM_OK;
+}
+
+// Training pass with the gather done by the step kernel: the index plan is uploaded once
+// (4 bytes per sample), then every step is a single launch that reads its rows from the placed
+// dataset (device memory, or host memory over PCIe).  Same results contract as pdm_engine_run.
+int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, int batch, const pdm_hyper* hyper,
+                          int ctas, float* step_results, float* device_ms) {
+  PDM_REQUIRE(e && indices && hyper, PDM_ERR_ARG, "pdm_engine_run_gather: engine, indices and hyper are required");
+  PDM_REQUIRE(e->params != nullptr, PDM_ERR_STATE, "pdm_engine_run_gather: pdm_engine_bind was not called");
+  PDM_REQUIRE(e->placed_mode >= 0, PDM_ERR_STATE, "pdm_engine_run_gather: pdm_engine_place_dataset was not called");
+  PDM_REQUIRE(batch >= 1, PDM_ERR_ARG, "pdm_engine_run_gather: batch must be >= 1");
+  if (count <= 0) return PDM_OK;
+  PDM_CHECK_CUDA(cudaSetDevice(e->device));
+  std::vector<int32_t> idx32((size_t)count);
+  for (int64_t i = 0; i < count; ++i) {
+    PDM_REQUIRE(indices[i] >= 0 && indices[i] < e->placed_n, PDM_ERR_ARG,
+                "pdm_engine_run_gather: index %lld at position %lld outside [0, %lld)", (long long)indices[i], (long long)i,
+                (long long)e->placed_n);
+    idx32[(size_t)i] = (int32_t)indices[i];
+  }
+  if (count > e->idx_cap) {
+    if (e->idx_dev) cudaFree(e->idx_dev);
+    e->idx_dev = nullptr;
+    e->idx_cap = 0;
+    PDM_CHECK_CUDA(cudaMalloc((void**)&e->idx_dev, (size_t)count * sizeof(int32_t)));
+    e->idx_cap = count;
+  }
+  const int64_t nsteps = (count + batch - 1) / batch;
+  int rc = ensure_results(e, nsteps);
+  if (rc != PDM_OK) return rc;
+  cudaStream_t cs = e->stream[0];
+  PDM_CHECK_CUDA(cudaEventRecord(e->ev_begin, cs));
+  PDM_CHECK_CUDA(cudaMemcpyAsync(e->idx_dev, idx32.data(), (size_t)count * sizeof(int32_t), cudaMemcpyHostToDevice, cs));
+  for (int64_t b = 0; b < nsteps; ++b) {
+    const int n = (int)std::min<int64_t>(batch, count - b * batch);
+    pdm_net_step_args a;
+    memset(&a, 0, sizeof(a));
+    a.x = e->placed_images;
+    a.x_dtype = PDM_U8;
+    a.y = e->placed_labels;
+    a.y_dtype = PDM_U8;
+    a.row_index = e->idx_dev + b * batch;
+    a.batch = n;
+    a.ctas = ctas;
+    a.params = e->params;
+    a.m = e->m;
+    a.v = e->v;
+    a.scratch = e->scratch;
+    a.sync = e->sync;
+    a.metrics = e->metrics;
+    a.step_out = e->host_results_dev + 2 * b;
+    a.hyper = *hyper;
+    a.hyper.step = hyper->step + b;
+    if (e->comm != nullptr) {
+      rc = pdm_comm_peers(e->comm, &a.peers, 1);
+      if (rc != PDM_OK) return rc;
+    }
+    rc = pdm_net_train_step(&a, cs);
+    if (rc != PDM_OK) return rc;
+  }
+  PDM_CHECK_CUDA(cudaEventRecord(e->ev_end, cs));
+  PDM_CHECK_CUDA(cudaStreamSynchronize(cs));     // idx32 must outlive the upload
+  if (device_ms) {
+    float ms = 0.f;
+    PDM_CHECK_CUDA(cudaEventElapsedTime(&ms, e->ev_begin, e->ev_end));
+    *device_ms = ms;
+  }
+  if (step_results) memcpy(step_results, e->host_results, (size_t)nsteps * 2 * sizeof(float));
+  return PDM_OK;
+}
+
 // Copy out {sum loss*n, correct, samples, 0}; reset != 0 zeroes the accumulator.  Synchronises.
 int pdm_engine_metrics(pdm_engine* e, double out[4], int reset) {
   PDM_REQUIRE(e && out, PDM_ERR_ARG, "pdm_engine_metrics: NULL argument");
@@ -535,6 +661,8 @@ int pdm_engine_destroy(pdm_engine* e) {
   if (e->ev_begin) cudaEventDestroy(e->ev_begin);
   if (e->ev_end) cudaEventDestroy(e->ev_end);
   if (e->host_results) cudaFreeHost(e->host_results);
+  unplace_dataset(e);
+  if (e->idx_dev) cudaFree(e->idx_dev);
   if (e->scratch) cudaFree(e->scratch);
   if (e->sync) cudaFree(e->sync);
   if (e->metrics) cudaFree(e->metrics);

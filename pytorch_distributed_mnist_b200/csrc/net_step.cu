@@ -80,6 +80,7 @@ struct KernelArgs {
   float* step_out;
   float* logits_out;
   long long* trace;   // optional [gridDim.x][8] clock64 stamps (bring-up / profiling aid)
+  const int* row_index;   // optional [batch]: batch row r is row row_index[r] of x / y (in-kernel gather)
   OptConsts oc;
   pdm_peers peers;
 };
@@ -197,7 +198,8 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
 #pragma unroll
   for (int r = 0; r < RT; ++r) {
     raw[r] = typename Raw::type();
-    if (owns_cols && row_begin + r < row_end) raw[r] = Raw::load(a.x, row_begin + r, tid);
+    if (owns_cols && row_begin + r < row_end)
+      raw[r] = Raw::load(a.x, a.row_index ? __ldg(a.row_index + row_begin + r) : row_begin + r, tid);
   }
 
   // Programmatic dependent launch: everything above overlaps the tail of the previous step's
@@ -228,7 +230,8 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
 
   for (int row0 = row_begin; row0 < row_end; row0 += RT) {
     const int nrows = min(RT, row_end - row0);
-    if (a.y != nullptr && tid < RT) sm.ys[tid] = tid < nrows ? load_label(a.y, a.y_dtype, row0 + tid) : 0;
+    if (a.y != nullptr && tid < RT)
+      sm.ys[tid] = tid < nrows ? load_label(a.y, a.y_dtype, a.row_index ? __ldg(a.row_index + row0 + tid) : row0 + tid) : 0;
 
     // decode this tile, prefetch the next one
     float xr[RT][4];
@@ -237,7 +240,7 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
 #pragma unroll
     for (int r = 0; r < RT; ++r) {
       const int nr = row0 + RT + r;
-      if (owns_cols && nr < row_end) raw[r] = Raw::load(a.x, nr, tid);
+      if (owns_cols && nr < row_end) raw[r] = Raw::load(a.x, a.row_index ? __ldg(a.row_index + nr) : nr, tid);
     }
 
     // ---- forward partials: v[r*10+c] = sum_i x[r][i] * W[c][i] ------------
@@ -709,6 +712,7 @@ extern "C" int pdm_net_train_step(const pdm_net_step_args* args, pdm_stream_t st
   ka.sync = args->sync;
   ka.metrics = args->metrics;
   ka.step_out = args->step_out;
+  ka.row_index = args->row_index;
   ka.oc = make_consts(h, world);
   ka.peers = args->peers;
   ka.peers.world = world;
@@ -897,6 +901,7 @@ extern "C" int pdm_net_train_step_static(const pdm_net_step_args* args, pdm_stre
   ka.sync = addrs.sync;
   ka.metrics = args->metrics;
   ka.step_out = args->step_out;
+  ka.row_index = args->row_index;
   ka.oc = make_consts(h, world);
   ka.peers = args->peers;
   ka.peers.world = world;

@@ -53,7 +53,7 @@ class NetStepArgs(ctypes.Structure):
                 ('params', c_void_p), ('m', c_void_p), ('v', c_void_p),
                 ('grad_out', c_void_p), ('scratch', c_void_p), ('sync', c_void_p),
                 ('metrics', c_void_p), ('step_out', c_void_p),
-                ('hyper', Hyper), ('peers', Peers)]
+                ('hyper', Hyper), ('peers', Peers), ('row_index', c_void_p)]
 
 
 class NativeError(RuntimeError):
@@ -99,6 +99,9 @@ def _declare(lib):
     lib.pdm_engine_run_device.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_int64, c_int, ctypes.c_int64,
                                           ctypes.POINTER(Hyper), c_int, ctypes.POINTER(c_float)]
     lib.pdm_engine_metrics.argtypes = [c_void_p, ctypes.POINTER(ctypes.c_double), c_int]
+    lib.pdm_engine_place_dataset.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_int64, c_int]
+    lib.pdm_engine_run_gather.argtypes = [c_void_p, c_void_p, ctypes.c_int64, c_int, ctypes.POINTER(Hyper), c_int,
+                                          c_void_p, ctypes.POINTER(c_float)]
     for nm in ('pdm_engine_scratch', 'pdm_engine_sync_words', 'pdm_engine_metrics_ptr'):
         getattr(lib, nm).restype = c_void_p
         getattr(lib, nm).argtypes = [c_void_p]

@@ -42,6 +42,7 @@ class NetEngine(object):
         _lib.check(self._lib.pdm_engine_bind(self._h, flat.params.data_ptr(), flat.exp_avg.data_ptr(),
                                              flat.exp_avg_sq.data_ptr(), comm_h), 'pdm_engine_bind')
         self._dataset = None
+        self._placed = None
         self.launches = 0       # kernels launched by this engine (bench bookkeeping)
 
     # -- dataset -------------------------------------------------------------
@@ -59,6 +60,28 @@ class NetEngine(object):
         self._dataset = (key, img, lab)
         _lib.check(self._lib.pdm_engine_set_dataset(self._h, img.ctypes.data, lab.ctypes.data, img.shape[0]),
                    'pdm_engine_set_dataset')
+        self._placed = None
+
+    PLACEMENTS = {'device': 0, 'zerocopy': 1}
+
+    def place_dataset(self, placement):
+        """Where the step kernel finds the training set (``set_dataset`` first):
+
+        ``'staged'``   (default) C++ loader threads gather each batch into pinned slots, one H2D copy per step
+        ``'device'``   the whole set is copied to HBM once; the kernel gathers its rows itself
+        ``'zerocopy'`` the host arrays are page-locked and mapped; the kernel gathers over PCIe
+        """
+        if placement == 'staged':
+            self._placed = None
+            return
+        if self._dataset is None:
+            raise RuntimeError('set_dataset() must be called before place_dataset()')
+        key, img, lab = self._dataset
+        if self._placed == (key, placement):
+            return
+        _lib.check(self._lib.pdm_engine_place_dataset(self._h, img.ctypes.data, lab.ctypes.data, img.shape[0],
+                                                      self.PLACEMENTS[placement]), 'pdm_engine_place_dataset')
+        self._placed = (key, placement)
 
     # -- runs ------------------------------------------------------------------
     def _indices(self, indices):
@@ -77,9 +100,14 @@ class NetEngine(object):
         ms = ctypes.c_float(0.0)
         h = self.optimizer.hyper(self.optimizer.step_count + 1)
         torch.cuda.current_stream(self.device).synchronize()
-        _lib.check(self._lib.pdm_engine_run(self._h, idx.ctypes.data, len(idx), int(batch), 1, ctypes.byref(h),
-                                            int(ctas), out.ctypes.data if out is not None else None,
-                                            ctypes.byref(ms)), 'pdm_engine_run(train)')
+        if getattr(self, '_placed', None) is not None:
+            _lib.check(self._lib.pdm_engine_run_gather(self._h, idx.ctypes.data, len(idx), int(batch), ctypes.byref(h),
+                                                       int(ctas), out.ctypes.data if out is not None else None,
+                                                       ctypes.byref(ms)), 'pdm_engine_run_gather')
+        else:
+            _lib.check(self._lib.pdm_engine_run(self._h, idx.ctypes.data, len(idx), int(batch), 1, ctypes.byref(h),
+                                                int(ctas), out.ctypes.data if out is not None else None,
+                                                ctypes.byref(ms)), 'pdm_engine_run(train)')
         self.optimizer.step_count += nsteps
         self.launches += nsteps
         if self.comm is not None and hasattr(self.comm, 'check_status'):

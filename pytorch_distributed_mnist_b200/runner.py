@@ -120,7 +120,8 @@ def _run(args):
                                   size=getattr(args, 'test_size', None), **data_kw)
 
     trainer = Trainer(model, optimizer, train_loader, test_loader, device,
-                      fused=getattr(args, 'fused', 'auto'))
+                      fused=getattr(args, 'fused', 'auto'),
+                      data_placement=getattr(args, 'data_placement', 'staged'))
     chk_dir = getattr(args, 'checkpoint_dir', None) or ckpt.CHECKPOINT_DIR
     try:
         if args.evaluate:

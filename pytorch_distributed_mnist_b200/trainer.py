@@ -34,13 +34,16 @@ def _unwrap(model):
 class Trainer(object):
 
     def __init__(self, model, optimizer, train_loader, test_loader, device, fused='auto', ctas=0,
-                 loader_workers=None):
+                 loader_workers=None, data_placement='staged'):
         self.model = model
         self.optimizer = optimizer
         self.train_loader = train_loader
         self.test_loader = test_loader
         self.device = torch.device(device)
         self.ctas = ctas
+        if data_placement not in ('staged', 'device', 'zerocopy'):
+            raise ValueError('data_placement must be staged, device or zerocopy')
+        self.data_placement = data_placement     # fused path only; see NetEngine.place_dataset
         self.engine = None
         self.last_train_ms = None      # device time of the last fused epoch
         self._metrics = None
@@ -81,6 +84,7 @@ class Trainer(object):
         if self.engine is not None:
             loader = self.train_loader
             self.engine.set_dataset(loader.images, loader.labels)
+            self.engine.place_dataset(self.data_placement)
             idx = loader.epoch_indices()
             steps, ms = self.engine.train(idx, loader.batch_size, ctas=self.ctas)
             self.last_train_ms = ms
@@ -111,7 +115,7 @@ class Trainer(object):
         test_acc = Accuracy()
         if self.engine is not None:
             loader = self.test_loader
-            self.engine.set_dataset(loader.images, loader.labels)
+            self.engine.set_dataset(loader.images, loader.labels)     # evaluation is sequential: staged path
             self.engine.metrics(reset=True)
             self.engine.evaluate(loader.epoch_indices(), loader.batch_size)
             loss_sum, correct, samples = self.engine.metrics(reset=True)

@@ -160,3 +160,24 @@ def test_fused_and_generic_paths_agree(free_port):
         torch.testing.assert_close(f[4], g[4], rtol=1e-3, atol=2e-4)
     finally:
         dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('placement', ['device', 'zerocopy'])
+def test_in_kernel_gather_matches_staged_path(placement):
+    """Same index plan through the pinned-ring path and through the in-kernel gather (dataset in
+    HBM / read from pinned host memory over PCIe): identical per-step results and parameters."""
+    from pytorch_distributed_mnist_b200.ops.engine import NetEngine
+    images, labels = _make(3000)
+    idx = torch.randperm(3000, generator=torch.Generator().manual_seed(5))[:2900]
+    outs = []
+    for mode in ('staged', placement):
+        net, fopt, _, _ = _build()
+        eng = NetEngine(fopt.flat, fopt, max_batch=128, slots=4, workers=2)
+        eng.set_dataset(images, labels)
+        eng.place_dataset(mode)
+        steps, ms = eng.train(idx, 128)
+        assert ms > 0 and steps.shape == (23, 2)
+        outs.append((steps.copy(), fopt.flat.params.clone()))
+        eng.close()
+    assert np.array_equal(outs[0][0], outs[1][0])
+    assert torch.equal(outs[0][1], outs[1][1])
