@@ -169,7 +169,7 @@ def run_ours(opts):
     timed_loader = pdm.MNISTDataLoader('unused', B, num_workers=opts.workers, train=True, synthetic=True,
                                        seed=4321, samples_per_epoch=K * B)
     trainer = pdm.Trainer(model, optimizer, warm_loader, warm_loader, device, fused='on', ctas=opts.ctas,
-                          loader_workers=opts.workers)
+                          loader_workers=opts.workers, data_placement=opts.placement)
     engine = trainer.engine
 
     # device-resident pool for the kernel-only number
@@ -221,9 +221,19 @@ def run_ours(opts):
                        POOL_BATCHES, POOL_BATCHES * B * 785 / 1e6)},
         'wall_ms_per_step': wall_ms / K,
         'clocks': clk,
-        'e2e': {'value': e2e_value, 'unit': 'images/s', 'h2d_bytes_per_step': B * 785, 'd2h_bytes_per_step': 8,
+        'e2e': {'value': e2e_value, 'unit': 'images/s',
+                'h2d_bytes_per_step': B * 785 + (B * 4 if trainer.data_placement == 'zerocopy' else 0),
+                'd2h_bytes_per_step': 8,
                 'ms_per_step': e2e_dev_ms / K, 'wall_ms_per_step': e2e_wall_ms / K, 'steps': K,
-                'api': 'Trainer.train() over MNISTDataLoader (pinned staging ring -> cudaMemcpyAsync per step)',
+                'api': 'Trainer.train() over MNISTDataLoader',
+                'input_path': {
+                    'staged': 'loader threads gather each shuffled batch into a pinned slot; one cudaMemcpyAsync H2D '
+                              '(B*785 bytes) per step',
+                    'zerocopy': 'the step kernel loads its shuffled rows (B*785 bytes) every step straight from the '
+                                'page-locked (cudaHostRegister) host dataset over PCIe; index plan uploaded as B*4 bytes/step',
+                }.get(trainer.data_placement, trainer.data_placement),
+                'result_path': 'kernel stores {loss, correct} (8 bytes) into mapped pinned host memory every step',
+                'host_cores_per_rank': (os.cpu_count() or 0) // max(1, world),
                 'final_loss': loss_avg.average},
         'gpu_launches': launches,
         'impl': 'ours',
@@ -353,6 +363,8 @@ def main():
     ap.add_argument('--workers', type=int, default=6, help='loader threads per rank (ours)')
     ap.add_argument('--ctas', type=int, default=0, help='CTAs of the fused step kernel (0 = from batch)')
     ap.add_argument('--comm', choices=('auto', 'peer', 'group'), default='auto')
+    ap.add_argument('--placement', choices=('auto', 'staged', 'zerocopy'), default='auto',
+                    help='e2e input path (ours); both move every step\'s inputs from pinned host memory')
     opts = ap.parse_args()
     if opts.steps < 1:
         raise SystemExit('--steps must be >= 1')

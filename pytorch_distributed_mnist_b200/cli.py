@@ -73,9 +73,10 @@ def build_parser():
                              'our native TCP store on the port after --init-method\'s')
     parser.add_argument('--fused', choices=('auto', 'on', 'off'), default='auto',
                         help='fused single-kernel training step for the reference Net')
-    parser.add_argument('--data-placement', choices=('staged', 'device', 'zerocopy'), default='staged',
+    parser.add_argument('--data-placement', choices=('auto', 'staged', 'device', 'zerocopy'), default='auto',
                         help='fused Net path: staged = pinned ring + one H2D copy per step; device = training set '
-                             'resident in HBM, gathered in-kernel; zerocopy = kernel gathers from pinned host memory')
+                             'resident in HBM, gathered in-kernel; zerocopy = kernel gathers from pinned host memory; '
+                             'auto = staged when the host has >= 6 cores per rank, else zerocopy')
     parser.add_argument('--checkpoint-dir', type=str, default=None, help='default: ./checkpoints (ref:264)')
     return parser
 

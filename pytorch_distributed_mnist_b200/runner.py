@@ -121,7 +121,7 @@ def _run(args):
 
     trainer = Trainer(model, optimizer, train_loader, test_loader, device,
                       fused=getattr(args, 'fused', 'auto'),
-                      data_placement=getattr(args, 'data_placement', 'staged'))
+                      data_placement=getattr(args, 'data_placement', 'auto'))
     chk_dir = getattr(args, 'checkpoint_dir', None) or ckpt.CHECKPOINT_DIR
     try:
         if args.evaluate:
