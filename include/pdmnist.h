@@ -244,6 +244,12 @@ int pdm_bias_relu(float* z, const float* bias, int64_t rows, int cols, pdm_strea
 /* dir 0: w [Co][Ci][9] -> a [Co][9][Ci], b [Ci][9][Co] (b may be NULL);  dir 1: a [Co][Ci][9] += src [Co][9][Ci]. */
 int pdm_conv_relayout(const float* src, float* a, float* b, int cout, int cin, int dir, pdm_stream_t stream);
 
+/* Reducer bucket assignment (c10d _compute_bucket_assignment_by_size): reverse parameter
+ * order, a bucket closes once it reaches its cap, the first bucket uses first_cap_bytes.
+ * out_bucket[i] = bucket of parameter i; returns the number of buckets. */
+int pdm_assign_buckets(const int64_t* numels, int n, int64_t first_cap_bytes, int64_t cap_bytes,
+                       int elem_size, int32_t* out_bucket);
+
 /* ------------------------------------------------------------------------
  * Peer-memory communicator (comm.cu).  Replaces ProcessGroupNCCL + NCCL +
  * the c10d Reducer on the gradient path (ref:167-168, ref:188-189, ref:91;

@@ -27,3 +27,30 @@ extern "C" int pdm_device_ok(int device) {
   }
   return major == 10 ? 1 : 0;
 }
+
+// Bucket assignment of the gradient reducer (the role of c10d's
+// _compute_bucket_assignment_by_size): walk the parameters in REVERSE order (gradients
+// become ready back to front), close a bucket once it reaches its byte cap; the first bucket uses
+// the small cap so communication starts early.  out_bucket[i] = bucket index of parameter i.
+// Returns the number of buckets, or a negative status.
+extern "C" int pdm_assign_buckets(const int64_t* numels, int n, int64_t first_cap_bytes, int64_t cap_bytes,
+                                  int elem_size, int32_t* out_bucket) {
+  PDM_REQUIRE(numels && out_bucket && n >= 1 && elem_size >= 1 && first_cap_bytes >= 1 && cap_bytes >= 1, PDM_ERR_ARG,
+              "pdm_assign_buckets: bad arguments");
+  int bucket = 0;
+  int64_t bytes = 0, cap = first_cap_bytes;
+  bool open = false;
+  for (int i = n - 1; i >= 0; --i) {
+    PDM_REQUIRE(numels[i] >= 0, PDM_ERR_ARG, "pdm_assign_buckets: negative size at %d", i);
+    out_bucket[i] = bucket;
+    bytes += numels[i] * elem_size;
+    open = true;
+    if (bytes >= cap) {
+      bucket += 1;
+      bytes = 0;
+      cap = cap_bytes;
+      open = false;
+    }
+  }
+  return bucket + (open ? 1 : 0);
+}

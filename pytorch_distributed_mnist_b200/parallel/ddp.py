@@ -53,6 +53,9 @@ def assign_buckets(numels, first_cap_bytes=FIRST_BUCKET_BYTES, cap_bytes=DEFAULT
     become ready back to front).  Returns a list of lists of indices; each inner list is
     a run of consecutive indices in descending order.  A bucket closes once it has
     reached its cap (the first bucket uses the small cap so communication starts early)."""
+    native = _native_assign(numels, first_cap_bytes, cap_bytes, elem_size)
+    if native is not None:
+        return native
     buckets, cur, cur_bytes = [], [], 0
     cap = first_cap_bytes
     for i in reversed(range(len(numels))):
@@ -64,6 +67,30 @@ def assign_buckets(numels, first_cap_bytes=FIRST_BUCKET_BYTES, cap_bytes=DEFAULT
     if cur:
         buckets.append(cur)
     return buckets
+
+
+def _native_assign(numels, first_cap_bytes, cap_bytes, elem_size):
+    """The same assignment computed by the native core (``pdm_assign_buckets``); None if unavailable."""
+    try:
+        import ctypes
+        from ..ops import _lib
+        lib = _lib.lib()
+        if not hasattr(lib, 'pdm_assign_buckets') or not numels:
+            return None
+        n = len(numels)
+        arr = (ctypes.c_int64 * n)(*[int(v) for v in numels])
+        out = (ctypes.c_int32 * n)()
+        lib.pdm_assign_buckets.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int64,
+                                           ctypes.c_int, ctypes.c_void_p]
+        nb = lib.pdm_assign_buckets(arr, n, int(first_cap_bytes), int(cap_bytes), int(elem_size), out)
+        if nb < 1:
+            return None
+        buckets = [[] for _ in range(nb)]
+        for i in reversed(range(n)):
+            buckets[out[i]].append(i)
+        return buckets
+    except Exception:  # noqa: BLE001 - the pure-Python path below is equivalent
+        return None
 
 
 def _shape_digest(params):

@@ -25,6 +25,7 @@ from .models.net import Net
 from .ops import _lib
 from .ops.loss import cross_entropy
 from .optim import _FusedBase
+from .utils.timing import nvtx_range
 
 
 def _unwrap(model):
@@ -85,6 +86,10 @@ class Trainer(object):
 
     # ------------------------------------------------------------------ train
     def train(self):
+        with nvtx_range('pdm.train_epoch'):
+            return self._train()
+
+    def _train(self):
         self.model.train()
         train_loss = Average()
         train_acc = Accuracy()
@@ -117,6 +122,10 @@ class Trainer(object):
     # --------------------------------------------------------------- evaluate
     @torch.no_grad()
     def evaluate(self):
+        with nvtx_range('pdm.evaluate'):
+            return self._evaluate()
+
+    def _evaluate(self):
         self.model.eval()
         test_loss = Average()
         test_acc = Accuracy()

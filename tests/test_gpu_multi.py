@@ -206,3 +206,36 @@ def test_full_job_spawn_nccl_peer(tmp_path, free_port):
         # every rank evaluates the full test set with identical parameters
         assert h[1]['test_acc'] == hists[0][1]['test_acc'] and abs(h[1]['test_loss'] - hists[0][1]['test_loss']) < 1e-9
     assert os.path.isfile(str(tmp_path / 'checkpoint_1.pth.tar'))
+
+
+def _timeout_worker(rank, world, port):
+    import time
+    from pytorch_distributed_mnist_b200.parallel.peer import PeerComm
+    _init(rank, world, port)
+    try:
+        dev = torch.device('cuda', rank)
+        comm = PeerComm(rank, world, dev, data_bytes=4096, timeout_s=1.0)
+        comm.barrier()                                   # everyone: a good collective first
+        torch.cuda.synchronize()
+        assert comm.status() == 0
+        if rank == 0:
+            t0 = time.time()
+            comm.barrier()                               # the peers never join this one
+            torch.cuda.synchronize()                     # returns: the wait is bounded, the GPU is not hung
+            assert time.time() - t0 < 20
+            st = comm.status()
+            assert st != 0 and 1 <= st - 1 < world, st   # 1 + a rank that did not show up
+            with pytest.raises(RuntimeError, match='did not reach a collective'):
+                comm.check_status()
+        else:
+            time.sleep(4.0)                              # "dead" peer: skips the collective
+        dist.barrier()
+        comm.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_dead_peer_is_reported_not_hung(free_port):
+    """a rank that never reaches a collective must produce a diagnosable error
+    on its peers (bounded device-side wait + status word), not a hung GPU."""
+    mp.spawn(_timeout_worker, args=(2, free_port), nprocs=2)
