@@ -441,68 +441,70 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
       acc.z += __shfl_xor_sync(0xffffffffu, acc.z, off);
       acc.w += __shfl_xor_sync(0xffffffffu, acc.w, off);
     }
-    if (!valid || sub != 0) continue;
-    if (j == kFlat4 - 1) {
+    // after the xor tree every lane of the group holds the same total
+    if (valid && j == kFlat4 - 1) {
       // lanes z, w of the last float4 are this rank's {sum of losses, correct}
-      if (a.step_out != nullptr) {
-        a.step_out[0] = acc.z * a.inv_batch;
-        a.step_out[1] = acc.w;
-      }
-      if (a.metrics != nullptr) {
-        a.metrics[0] += (double)acc.z;
-        a.metrics[1] += (double)acc.w;
-        a.metrics[2] += (double)a.batch;
+      if (sub == 0) {
+        if (a.step_out != nullptr) {
+          a.step_out[0] = acc.z * a.inv_batch;
+          a.step_out[1] = acc.w;
+        }
+        if (a.metrics != nullptr) {
+          a.metrics[0] += (double)acc.z;
+          a.metrics[1] += (double)acc.w;
+          a.metrics[2] += (double)a.batch;
+        }
       }
       acc.z = 0.f;
       acc.w = 0.f;
     }
 
     if (W > 1) {
+      // The 8 lanes of a group split the peers: lane `sub` pushes this float4 to rank `sub` and
+      // polls rank `sub`'s slot in our inbox, so the per-peer stores and waits run side by side
+      // instead of one lane walking all peers.  The sum is then formed in rank order from the
+      // lanes' values, identically on every rank.
       const size_t par = (size_t)(seq & 1u) * W;
-      const size_t slot = ((par + a.peers.rank) * kFlat4 + j) * 4;
-      for (int p = 0; p < W; ++p) {
-        if (p == a.peers.rank) continue;
-        uint64_t* dst = a.peers.inbox[p] + slot;
+      const bool remote = valid && sub < W && sub != a.peers.rank;
+      if (remote) {
+        uint64_t* dst = a.peers.inbox[sub] + ((par + a.peers.rank) * kFlat4 + j) * 4;
         ll_store2(dst, acc.x, acc.y, seq);
         ll_store2(dst + 2, acc.z, acc.w, seq);
       }
-      // Poll every peer's slot in the same pass (loads to all of them in flight together), keep a
-      // bit per peer still missing, then add in rank order so every rank computes the same sum.
-      const uint64_t* inbox = a.peers.inbox[a.peers.rank];
-      float4 q[PDM_MAX_RANKS];
-      uint32_t pending = ((1u << W) - 1u) & ~(1u << a.peers.rank);   // bit p: peer p's slot not complete yet
-      uint32_t half_ok = 0;                                          // bits [2p, 2p+1]: halves already valid
-      uint64_t t0 = 0;
-      uint32_t spins = 0;
-      while (pending != 0u) {
-#pragma unroll
-        for (int p = 0; p < PDM_MAX_RANKS; ++p) {
-          if (p < W && (pending >> p) & 1u) {
-            const uint64_t* s = inbox + ((par + p) * kFlat4 + j) * 4;
-            if (!((half_ok >> (2 * p)) & 1u) && ll_load2(s, seq, q[p].x, q[p].y)) half_ok |= 1u << (2 * p);
-            if (!((half_ok >> (2 * p + 1)) & 1u) && ll_load2(s + 2, seq, q[p].z, q[p].w)) half_ok |= 2u << (2 * p);
-            if (((half_ok >> (2 * p)) & 3u) == 3u) pending &= ~(1u << p);
-          }
-        }
-        if (pending != 0u && (++spins & 1023u) == 0u && a.peers.timeout_ns != 0) {
-          const uint64_t now = globaltimer_ns();
-          if (t0 == 0) t0 = now;
-          else if (now - t0 > a.peers.timeout_ns) {
-            if (a.peers.status != nullptr) atomicExch(a.peers.status, 1 + __ffs(pending) - 1);
-            break;
+      float4 q = (valid && sub == a.peers.rank) ? acc : make_float4(0.f, 0.f, 0.f, 0.f);
+      if (remote) {
+        const uint64_t* src = a.peers.inbox[a.peers.rank] + ((par + sub) * kFlat4 + j) * 4;
+        bool ok0 = false, ok1 = false;
+        uint64_t t0 = 0;
+        uint32_t spins = 0;
+        while (true) {
+          if (!ok0) ok0 = ll_load2(src, seq, q.x, q.y);
+          if (!ok1) ok1 = ll_load2(src + 2, seq, q.z, q.w);
+          if (ok0 && ok1) break;
+          if ((++spins & 1023u) == 0u && a.peers.timeout_ns != 0) {
+            const uint64_t now = globaltimer_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > a.peers.timeout_ns) {
+              if (a.peers.status != nullptr) atomicExch(a.peers.status, 1 + sub);
+              break;
+            }
           }
         }
       }
       float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+      const int group_base = lane & ~7;
 #pragma unroll
       for (int p = 0; p < PDM_MAX_RANKS; ++p) {
-        if (p < W) {
-          const float4 t4 = p == a.peers.rank ? acc : q[p];
-          sum.x += t4.x; sum.y += t4.y; sum.z += t4.z; sum.w += t4.w;
-        }
+        const float tx = __shfl_sync(0xffffffffu, q.x, group_base + p);
+        const float ty = __shfl_sync(0xffffffffu, q.y, group_base + p);
+        const float tz = __shfl_sync(0xffffffffu, q.z, group_base + p);
+        const float tw = __shfl_sync(0xffffffffu, q.w, group_base + p);
+        if (p < W) { sum.x += tx; sum.y += ty; sum.z += tz; sum.w += tw; }
       }
       acc = sum;
     }
+    if (!valid || sub != 0) continue;
+
     const float iw = a.oc.inv_world;
     acc.x *= iw; acc.y *= iw; acc.z *= iw; acc.w *= iw;
     if (a.grad_out != nullptr) *reinterpret_cast<float4*>(a.grad_out + 4 * j) = acc;
