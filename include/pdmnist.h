@@ -99,7 +99,7 @@ typedef struct pdm_peers {
  *           v may be NULL for SGD)
  *  grad_out optional PDM_NET_FLAT floats: receives the reduced mean gradient
  *  scratch  PDM_NET_SCRATCH_FLOATS(ctas) floats of device scratch
- *  sync     2 x uint32 device words, zero-initialised once (grid barrier)
+ *  sync     3 x uint32 device words, zero-initialised once (grid barrier + step-to-step flag)
  *  metrics  optional 4 doubles, device: += {loss*B, correct, B, 0}
  *  step_out optional 2 floats, device or mapped host: {mean loss, #correct}
  *  ctas     0 = choose from B; else 1..PDM_NET_MAX_CTAS
@@ -122,11 +122,18 @@ typedef struct pdm_net_step_args {
   const int32_t* row_index;   /* optional, device: batch row r is row row_index[r] of x and y.  Lets the
                                  kernel gather a shuffled batch itself from a dataset that is resident in
                                  device memory -- or in pinned, mapped host memory (zero-copy over PCIe). */
+  int32_t flag_dependency;    /* 1: order this step after the previous one through sync[2] (a count of finished
+                                 CTAs) instead of waiting for the previous grid to be complete and flushed --
+                                 lets the remote stores of step n drain under step n+1.  Needs `sync` to be at
+                                 least 3 words and done_before to be exact. */
+  uint32_t done_before;       /* sum of pdm_net_planned_ctas() over all earlier steps issued on these sync words */
 } pdm_net_step_args;
 
 int pdm_net_train_step(const pdm_net_step_args* args, pdm_stream_t stream);
 /* CTAs pdm_net_train_step will launch for a batch when args->ctas == 0. */
 int pdm_net_default_ctas(int batch);
+/* CTAs it will launch for (batch, args->ctas). */
+int pdm_net_planned_ctas(int batch, int want_ctas);
 
 /* The same fused step for callers that must not allocate.  (This entry point has no
  * counterpart in the reference, which ships no native code and never manages device memory.)

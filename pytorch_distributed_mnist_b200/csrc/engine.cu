@@ -86,6 +86,7 @@ struct pdm_engine {
   uint32_t* sync = nullptr;
   double* metrics = nullptr;
   float* step_out = nullptr;              // [slots][2]
+  uint32_t done_total = 0;                // CTAs launched so far on `sync` (step-to-step flag dependency)
   std::vector<uint8_t*> dev_slot;         // [slots] packed batch
   std::vector<uint8_t*> host_slot;        // [slots] pinned staging
   float* host_results = nullptr;          // pinned + mapped [capacity][2]
@@ -388,7 +389,10 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
         rc = pdm_comm_peers(e->comm, &a.peers, 1);
         if (rc != PDM_OK) break;
       }
+      a.flag_dependency = 1;
+      a.done_before = e->done_total;
       rc = pdm_net_train_step(&a, cs);
+      if (rc == PDM_OK) e->done_total += (uint32_t)pdm_net_planned_ctas(n, ctas);
     } else {
       rc = pdm_net_eval_step(e->dev_slot[s], PDM_U8, e->dev_slot[s] + (size_t)n * kImg, PDM_U8, n, e->params, nullptr,
                              e->metrics, cs);
@@ -495,8 +499,11 @@ int pdm_engine_run_device(pdm_engine* e, const uint8_t* dev_images, const uint8_
       int rc = pdm_comm_peers(e->comm, &a.peers, 1);
       if (rc != PDM_OK) return rc;
     }
+    a.flag_dependency = 1;
+    a.done_before = e->done_total;
     int rc = pdm_net_train_step(&a, st);
     if (rc != PDM_OK) return rc;
+    e->done_total += (uint32_t)pdm_net_planned_ctas(batch, ctas);
   }
   PDM_CHECK_CUDA(cudaEventRecord(e->ev_end, st));
   PDM_CHECK_CUDA(cudaStreamSynchronize(st));
@@ -611,8 +618,11 @@ int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, 
       rc = pdm_comm_peers(e->comm, &a.peers, 1);
       if (rc != PDM_OK) return rc;
     }
+    a.flag_dependency = 1;
+    a.done_before = e->done_total;
     rc = pdm_net_train_step(&a, cs);
     if (rc != PDM_OK) return rc;
+    e->done_total += (uint32_t)pdm_net_planned_ctas(n, ctas);
   }
   PDM_CHECK_CUDA(cudaEventRecord(e->ev_end, cs));
   PDM_CHECK_CUDA(cudaStreamSynchronize(cs));     // idx32 must outlive the upload

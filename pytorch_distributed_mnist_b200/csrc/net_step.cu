@@ -81,6 +81,8 @@ struct KernelArgs {
   float* logits_out;
   long long* trace;   // optional [gridDim.x][8] clock64 stamps (bring-up / profiling aid)
   const int* row_index;   // optional [batch]: batch row r is row row_index[r] of x / y (in-kernel gather)
+  int flag_dep;           // 1: wait for the previous step through sync[2] instead of griddepcontrol.wait
+  uint32_t done_before;   // value sync[2] reaches once every CTA of every earlier launch has finished
   OptConsts oc;
   pdm_peers peers;
 };
@@ -205,7 +207,22 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
   // Programmatic dependent launch: everything above overlaps the tail of the previous step's
   // kernel; parameters, optimizer state, scratch and barrier words are only touched below.
   // (A no-op when the kernel was not launched with the PDL attribute.)
-  if (MODE == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
+  //
+  // Two ways to wait for the previous step.  griddepcontrol.wait waits for that grid to be
+  // complete *and flushed*, which with peers includes the acknowledgement of its remote LL
+  // stores (measured ~4-5 us per step at 2 GPUs).  The flag form only waits until all of its
+  // CTAs have finished phase 2 (each bumps sync[2] after its last local store, release/acquire
+  // at gpu scope), so remote traffic of step n drains under step n+1.
+  if (MODE == 0) {
+    if (a.flag_dep) {
+      if (tid == 0) {
+        while ((int32_t)(ld_acquire_gpu(a.sync + 2) - a.done_before) < 0) { }
+      }
+      __syncthreads();
+    } else {
+      asm volatile("griddepcontrol.wait;" ::: "memory");
+    }
+  }
 
   uint32_t bar_base = 0;
   if (MODE == 0 && tid == 0 && G > 1) bar_base = ld_acquire_gpu(a.sync + 1);   // latency hidden by phase 1
@@ -528,6 +545,11 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
     }
   }
   __syncthreads();
+  if (tid == 0) {
+    // this CTA is done with parameters, optimizer state, scratch and inbox: tell the next step
+    __threadfence();
+    asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(a.sync + 2) : "memory");
+  }
   PDM_TRACE(4);
 #undef PDM_TRACE
 }
@@ -670,6 +692,12 @@ extern "C" int pdm_net_default_ctas(int batch) {
   return g;
 }
 
+extern "C" int pdm_net_planned_ctas(int batch, int want_ctas) {
+  int g, act, rpc;
+  plan_rows(batch, want_ctas, &g, &act, &rpc);
+  return g;
+}
+
 extern "C" int pdm_net_train_step(const pdm_net_step_args* args, pdm_stream_t stream) {
   PDM_REQUIRE(args != nullptr, PDM_ERR_ARG, "pdm_net_train_step: args is NULL");
   PDM_REQUIRE(args->batch >= 1, PDM_ERR_ARG, "pdm_net_train_step: batch must be >= 1 (got %d)", args->batch);
@@ -715,6 +743,8 @@ extern "C" int pdm_net_train_step(const pdm_net_step_args* args, pdm_stream_t st
   ka.metrics = args->metrics;
   ka.step_out = args->step_out;
   ka.row_index = args->row_index;
+  ka.flag_dep = (args->flag_dependency && launch_mode() == LAUNCH_PDL) ? 1 : 0;
+  ka.done_before = args->done_before;
   ka.oc = make_consts(h, world);
   ka.peers = args->peers;
   ka.peers.world = world;
