@@ -30,8 +30,9 @@ def main():
         for c in [int(v) for v in a.ctas.split(',')]:
             eng.train_device(x, y, B, 50, ctas=c)
             ms = eng.train_device(x, y, B, a.steps, ctas=c)
-            print('batch {:5d} ctas {:3d} launch {} rt {}: {:7.2f} us/step  {:9.2f} M img/s'.format(
-                B, c, os.environ.get('PDM_NET_LAUNCH', 'pdl'), os.environ.get('PDM_NET_RT', 'auto'), ms * 1e3 / a.steps, B * a.steps / ms / 1e3), flush=True)
+            print('batch {:5d} ctas {:3d} launch {} rt {} dep {} trigger {} poll {}: {:7.2f} us/step  {:9.2f} M img/s'.format(
+                B, c, os.environ.get('PDM_NET_LAUNCH', 'pdl'), os.environ.get('PDM_NET_RT', 'auto'),
+                os.environ.get('PDM_NET_DEP', 'flag'), os.environ.get('PDM_NET_TRIGGER', 'start'), os.environ.get('PDM_NET_POLL_NS', '0'), ms * 1e3 / a.steps, B * a.steps / ms / 1e3), flush=True)
         eng.close()
 
 

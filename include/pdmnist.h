@@ -122,10 +122,11 @@ typedef struct pdm_net_step_args {
   const int32_t* row_index;   /* optional, device: batch row r is row row_index[r] of x and y.  Lets the
                                  kernel gather a shuffled batch itself from a dataset that is resident in
                                  device memory -- or in pinned, mapped host memory (zero-copy over PCIe). */
-  int32_t flag_dependency;    /* 1: order this step after the previous one through sync[2] (a count of finished
-                                 CTAs) instead of waiting for the previous grid to be complete and flushed --
-                                 lets the remote stores of step n drain under step n+1.  Needs `sync` to be at
-                                 least 3 words and done_before to be exact. */
+  int32_t flag_dependency;    /* 1: the caller can order this step after the previous one through sync[2] (a
+                                 count of finished CTAs) instead of grid completion, which would let the remote
+                                 stores of step n drain under step n+1.  Experimental: honoured only when the
+                                 process runs with PDM_NET_DEP=flag (it measured slower than the default on
+                                 B200).  Needs `sync` to be at least 3 words and done_before to be exact. */
   uint32_t done_before;       /* sum of pdm_net_planned_ctas() over all earlier steps issued on these sync words */
 } pdm_net_step_args;
 

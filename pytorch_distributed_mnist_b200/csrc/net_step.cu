@@ -83,6 +83,8 @@ struct KernelArgs {
   const int* row_index;   // optional [batch]: batch row r is row row_index[r] of x / y (in-kernel gather)
   int flag_dep;           // 1: wait for the previous step through sync[2] instead of griddepcontrol.wait
   uint32_t done_before;   // value sync[2] reaches once every CTA of every earlier launch has finished
+  int trigger_early;      // 1: release the next step's launch as soon as this grid is resident
+  int poll_ns;            // back-off between polls of sync[2]
   OptConsts oc;
   pdm_peers peers;
 };
@@ -179,6 +181,11 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
   const int cta = blockIdx.x;
   const int G = gridDim.x;
   const bool owns_cols = tid < kCols4;
+  // PDL secondary launches once EVERY CTA of this grid has executed launch_dependents, i.e. once the
+  // whole grid is resident -- exactly the condition under which the successor may take SMs without
+  // starving this grid's barrier.  Only with the flag dependency: the successor then orders itself
+  // after this step through sync[2], not through grid completion.
+  if (MODE == 0 && a.trigger_early) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 #define PDM_TRACE(slot) do { if (MODE == 0 && a.trace != nullptr && tid == 0) a.trace[cta * 8 + (slot)] = clock64(); } while (0)
   PDM_TRACE(0);
 
@@ -216,7 +223,9 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
   if (MODE == 0) {
     if (a.flag_dep) {
       if (tid == 0) {
-        while ((int32_t)(ld_acquire_gpu(a.sync + 2) - a.done_before) < 0) { }
+        while ((int32_t)(ld_acquire_gpu(a.sync + 2) - a.done_before) < 0) {
+          if (a.poll_ns > 0) __nanosleep(a.poll_ns);
+        }
       }
       __syncthreads();
     } else {
@@ -425,7 +434,7 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
   }
   // Let the next step's kernel start its input prefetch (PDL); it still waits for this grid to
   // finish before it touches parameters or scratch.
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (!a.trigger_early) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   PDM_TRACE(3);
 
   // ---- phase 2: reduce partials, all-reduce with peers, optimizer ----------
@@ -544,8 +553,8 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
       if (a.v != nullptr) *reinterpret_cast<float4*>(a.v + 4 * j) = v4;
     }
   }
-  __syncthreads();
-  if (tid == 0) {
+  if (a.flag_dep || a.trace != nullptr) __syncthreads();
+  if (a.flag_dep && tid == 0) {
     // this CTA is done with parameters, optimizer state, scratch and inbox: tell the next step
     __threadfence();
     asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(a.sync + 2) : "memory");
@@ -743,8 +752,18 @@ extern "C" int pdm_net_train_step(const pdm_net_step_args* args, pdm_stream_t st
   ka.metrics = args->metrics;
   ka.step_out = args->step_out;
   ka.row_index = args->row_index;
-  ka.flag_dep = (args->flag_dependency && launch_mode() == LAUNCH_PDL) ? 1 : 0;
-  ka.done_before = args->done_before;
+  {
+    // bring-up knobs: PDM_NET_DEP=grid|flag, PDM_NET_TRIGGER=barrier|start, PDM_NET_POLL_NS=<n>
+    // Measured on B200 (profiles/raw/step_sweep_dep.log): the flag dependency does not beat
+    // griddepcontrol.wait (10.3 vs 8.7 us/step on one GPU, 15.4 vs 14.8 on two), so it is opt-in.
+    static const int dep_flag = [] { const char* e = getenv("PDM_NET_DEP"); return (e && !strcmp(e, "flag")) ? 1 : 0; }();
+    static const int early = [] { const char* e = getenv("PDM_NET_TRIGGER"); return (e && !strcmp(e, "barrier")) ? 0 : 1; }();
+    static const int poll = [] { const char* e = getenv("PDM_NET_POLL_NS"); return e && *e ? atoi(e) : 0; }();
+    ka.flag_dep = (args->flag_dependency && dep_flag && launch_mode() == LAUNCH_PDL) ? 1 : 0;
+    ka.done_before = args->done_before;
+    ka.trigger_early = (ka.flag_dep && early) ? 1 : 0;
+    ka.poll_ns = poll;
+  }
   ka.oc = make_consts(h, world);
   ka.peers = args->peers;
   ka.peers.world = world;
