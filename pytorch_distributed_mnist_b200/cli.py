@@ -76,7 +76,7 @@ def build_parser():
     parser.add_argument('--data-placement', choices=('auto', 'staged', 'device', 'zerocopy'), default='auto',
                         help='fused Net path: staged = pinned ring + one H2D copy per step; device = training set '
                              'resident in HBM, gathered in-kernel; zerocopy = kernel gathers from pinned host memory; '
-                             'auto = staged when the host has >= 6 cores per rank, else zerocopy')
+                             'auto = staged when the host has >= 12 cores per rank, else zerocopy')
     parser.add_argument('--checkpoint-dir', type=str, default=None, help='default: ./checkpoints (ref:264)')
     return parser
 

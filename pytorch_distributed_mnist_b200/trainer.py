@@ -45,12 +45,12 @@ class Trainer(object):
         if data_placement not in ('auto', 'staged', 'device', 'zerocopy'):
             raise ValueError('data_placement must be auto, staged, device or zerocopy')
         if data_placement == 'auto':
-            # The staged path needs a few host cores per rank for its gather threads (measured:
-            # 15 us/step with 6 threads, 67 us/step with 2); when cores are scarce let the kernel
-            # gather straight from the page-locked dataset instead (19 us/step, no host work).
+            # The staged path needs host cores AND host memory bandwidth for its gather threads
+            # (measured per step: 14.5 us on 1 GPU, 19 us on 2, 39 us on 4, 71 us on 8 GPUs of a
+            # 32-core box); the zero-copy path needs neither (19 us on 1 GPU, 32 us on 8).
             import os
             world = getattr(model, 'world', 1)
-            data_placement = 'staged' if (os.cpu_count() or 1) // max(1, world) >= 6 else 'zerocopy'
+            data_placement = 'staged' if (os.cpu_count() or 1) // max(1, world) >= 12 else 'zerocopy'
         self.data_placement = data_placement     # fused path only; see NetEngine.place_dataset
         self.engine = None
         self.last_train_ms = None      # device time of the last fused epoch

@@ -30,7 +30,7 @@ eng.train(torch.randperm(300), 64)
 eng.evaluate(torch.arange(300), 64)
 eng.close()
 for a_mn, b_mn in ((False, False), (False, True), (True, True)):
-    A, Bm = torch.randn(130, 64, device=dev), torch.randn(48, 64, device=dev)
+    A, Bm = torch.randn(132, 64, device=dev), torch.randn(48, 64, device=dev)
     a = A.t().contiguous() if a_mn else A
     b = Bm.t().contiguous() if b_mn else Bm
     out = G.gemm(a, b, a_mn_major=a_mn, b_mn_major=b_mn)
