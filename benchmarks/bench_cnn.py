@@ -4,6 +4,8 @@
     python benchmarks/bench_cnn.py [--width 1] [--batch 512] [--steps 50] [--warmup 10]
     python -m torch.distributed.run --nproc-per-node N ... benchmarks/bench_cnn.py ...
 
+engine: the same kernels driven by the native step executor (csrc/cnn_step.cu, one C call per step;
+        the path Trainer.train() takes for --arch cnn).
 ours  : models.CNN on the hand-written kernels (tcgen05 implicit-GEMM conv, fused pool/dropout,
         tcgen05 fc1, fused fc2), our DistributedDataParallel (peer-memory bucketed all-reduce fused
         with Adam), fused cross-entropy.
@@ -29,10 +31,15 @@ def run(kind, a, rank, local, world, dev):
     from pytorch_distributed_mnist_b200.ops.loss import cross_entropy
     torch.manual_seed(0)
     model = pdm.CNN(width=a.width).to(dev)
-    if kind == 'ours':
+    eng = None
+    if kind in ('ours', 'engine'):
         ddp = pdm.DistributedDataParallel(model, device_ids=[local])
         opt = pdm.FusedAdam(ddp.parameters(), lr=1e-3)
         loss_fn = cross_entropy
+        if kind == 'engine':
+            # native step executor (csrc/cnn_step.cu): what Trainer.train() drives for --arch cnn
+            from pytorch_distributed_mnist_b200.ops.cnn_engine import CnnEngine
+            eng = CnnEngine(model, ddp.flat, opt, ddp=ddp, max_batch=a.batch)
     else:
         torch.backends.cuda.matmul.allow_tf32 = True
         torch.backends.cudnn.allow_tf32 = True
@@ -50,6 +57,8 @@ def run(kind, a, rank, local, world, dev):
     ys = [torch.randint(0, 10, (a.batch,), device=dev, generator=g) for _ in range(nb)]
 
     def step(i):
+        if eng is not None:
+            return eng.train_step(xs[i % nb], ys[i % nb], seed=i)
         out = ddp(xs[i % nb])
         loss = loss_fn(out, ys[i % nb])
         opt.zero_grad()
@@ -71,6 +80,8 @@ def run(kind, a, rank, local, world, dev):
     t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item()) / a.steps
+    if eng is not None:
+        eng.close()
     if hasattr(ddp, 'close'):
         ddp.close()
     return {'impl': kind, 'width': a.width, 'n_gpus': world, 'per_gpu_batch': a.batch, 'ms_per_step': ms,
@@ -94,7 +105,7 @@ def main():
     os.environ.setdefault('MASTER_PORT', '29577')
     dist.init_process_group('nccl', init_method='env://', world_size=world, rank=rank, device_id=dev)
     rows = []
-    for kind in (('ours', 'stock') if a.impl == 'both' else (a.impl,)):
+    for kind in (('engine', 'ours', 'stock') if a.impl == 'both' else tuple(a.impl.split(','))):
         r = run(kind, a, rank, local, world, dev)
         rows.append(r)
         if rank == 0:

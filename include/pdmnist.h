@@ -252,6 +252,37 @@ int pdm_bias_relu(float* z, const float* bias, int64_t rows, int cols, pdm_strea
 /* dir 0: w [Co][Ci][9] -> a [Co][9][Ci], b [Ci][9][Co] (b may be NULL);  dir 1: a [Co][Ci][9] += src [Co][9][Ci]. */
 int pdm_conv_relayout(const float* src, float* a, float* b, int cout, int cin, int dir, pdm_stream_t stream);
 
+/* ------------------------------------------------------------------------
+ * Native executor for one CNN step (cnn_step.cu): every kernel of the forward, loss and backward
+ * pass issued from one call, gradients written straight into the flat gradient buffer, and the
+ * reducer's per-bucket fused all-reduce + optimizer launched on a side stream as soon as a bucket
+ * is final (static schedule; the role of the c10d Reducer's hooks for this model).
+ * Parameter pointers follow the module's layout (conv weights [Co][Ci][3][3], fc weights [out][in]).
+ * ---------------------------------------------------------------------- */
+typedef struct pdm_cnn_ctx pdm_cnn_ctx;
+typedef struct pdm_cnn_params {
+  float *conv1_w, *conv1_b, *conv2_w, *conv2_b, *fc1_w, *fc1_b, *fc2_w, *fc2_b;
+} pdm_cnn_params;
+struct pdm_comm;
+typedef struct pdm_cnn_plan {
+  int32_t n_buckets;            /* 1..4, in launch order (bucket 0 = the LAST parameters) */
+  int32_t max_ctas;             /* CTAs for each reducer kernel (0 = default) */
+  int64_t lo[4], hi[4];         /* float ranges of the buckets inside the flat buffers */
+  struct pdm_comm* comm;        /* NULL: no peers, optimizer only */
+  size_t params_off, grads_off, m_off, v_off;   /* comm != NULL: byte offsets of the flat buffers in its data area */
+  float *params, *grads, *m, *v;                /* comm == NULL: the flat buffers themselves */
+  pdm_hyper hyper;
+  float grad_scale;             /* 1/world */
+} pdm_cnn_plan;
+int pdm_cnn_create(pdm_cnn_ctx** out, int device, int width, int max_batch);
+int pdm_cnn_eval_step(pdm_cnn_ctx* c, const void* x, int x_dtype, const void* y, int y_dtype, int batch,
+                      const pdm_cnn_params* params, float* logits_out, double* metrics, pdm_stream_t stream);
+int pdm_cnn_train_step(pdm_cnn_ctx* c, const void* x, int x_dtype, const void* y, int y_dtype, int batch,
+                       const pdm_cnn_params* params, const pdm_cnn_params* grads, float p1, float p2,
+                       uint64_t seed, double* metrics, float* loss_out, const pdm_cnn_plan* plan,
+                       pdm_stream_t stream);
+int pdm_cnn_destroy(pdm_cnn_ctx* c);
+
 /* Reducer bucket assignment (c10d _compute_bucket_assignment_by_size): reverse parameter
  * order, a bucket closes once it reaches its cap, the first bucket uses first_cap_bytes.
  * out_bucket[i] = bucket of parameter i; returns the number of buckets. */

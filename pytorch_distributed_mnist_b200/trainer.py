@@ -53,6 +53,7 @@ class Trainer(object):
             data_placement = 'staged' if (os.cpu_count() or 1) // max(1, world) >= 12 else 'zerocopy'
         self.data_placement = data_placement     # fused path only; see NetEngine.place_dataset
         self.engine = None
+        self.cnn_engine = None         # native CNN step executor (ops.cnn_engine)
         self.last_train_ms = None      # device time of the last fused epoch
         self._metrics = None
         want = fused in ('auto', True, 'on')
@@ -63,6 +64,12 @@ class Trainer(object):
             comm = getattr(model, 'comm', None) if getattr(model, 'uses_peer', False) else None
             self.engine = NetEngine(self.optimizer.flat, self.optimizer, comm=comm, device=self.device,
                                     max_batch=max_batch, slots=8, workers=workers)
+        elif want and self._cnn_eligible():
+            from .ops.cnn_engine import CnnEngine
+            ddp = self.model if hasattr(self.model, 'buckets') else None
+            max_batch = max(train_loader.batch_size, test_loader.batch_size if test_loader is not None else 1)
+            self.cnn_engine = CnnEngine(_unwrap(self.model), self.optimizer.flat, self.optimizer, ddp=ddp,
+                                        max_batch=max_batch)
         elif fused in (True, 'on'):
             raise RuntimeError('fused path requested but not available: needs a CUDA device, the native library, '
                                'the reference Net, a Fused optimizer and MNISTDataLoader inputs')
@@ -83,6 +90,31 @@ class Trainer(object):
             return False       # stock-collective fallback: gradients go through torch.distributed
         _lib.lib()             # on a GPU box a missing native library is an error, not a fallback
         return True
+
+    def _cnn_eligible(self):
+        from .models.cnn import CNN
+        from .ops import cnn_ops
+        if self.device.type != 'cuda' or not torch.cuda.is_available():
+            return False
+        cnn = _unwrap(self.model)
+        if not isinstance(cnn, CNN) or cnn.width > 8 or not isinstance(self.optimizer, _FusedBase):
+            return False
+        if not self.optimizer.flat.params.is_cuda or len(self.optimizer.flat.param_list) != 8:
+            return False
+        world = getattr(self.model, 'world', 1)
+        if world > 1 and not getattr(self.model, 'uses_peer', False):
+            return False
+        return cnn_ops.available()
+
+    def _batches(self, loader):
+        """(data, target) on the device; raw uint8 when the loader can provide it (4x less PCIe
+        traffic, normalisation happens in conv1)."""
+        if self.cnn_engine is not None and isinstance(loader, MNISTDataLoader):
+            for img, lab in loader.raw_batches():
+                yield img.to(self.device, non_blocking=True), lab.to(self.device, non_blocking=True)
+        else:
+            for data, target in loader:
+                yield data.to(self.device, non_blocking=True), target.to(self.device, non_blocking=True)
 
     # ------------------------------------------------------------------ train
     def train(self):
@@ -106,6 +138,15 @@ class Trainer(object):
                 b = min(loader.batch_size, n - i * loader.batch_size)
                 train_loss.update(float(steps[i, 0]), b)
                 train_acc.update_counts(int(round(float(steps[i, 1]))), b)
+            return train_loss, train_acc
+
+        if self.cnn_engine is not None:
+            self.cnn_engine.read_metrics(reset=True)
+            for data, target in self._batches(self.train_loader):
+                self.cnn_engine.train_step(data, target)
+            loss_sum, correct, samples = self.cnn_engine.read_metrics(reset=True)
+            train_loss.update_sum(loss_sum, samples)
+            train_acc.update_counts(correct, samples)
             return train_loss, train_acc
 
         dm = self._device_metrics()
@@ -139,6 +180,15 @@ class Trainer(object):
             test_acc.update_counts(correct, samples)
             return test_loss, test_acc
 
+        if self.cnn_engine is not None:
+            self.cnn_engine.read_metrics(reset=True)
+            for data, target in self._batches(self.test_loader):
+                self.cnn_engine.eval_step(data, target)
+            loss_sum, correct, samples = self.cnn_engine.read_metrics(reset=True)
+            test_loss.update_sum(loss_sum, samples)
+            test_acc.update_counts(correct, samples)
+            return test_loss, test_acc
+
         dm = self._device_metrics()
         for data, target in self.test_loader:
             data = data.to(self.device, non_blocking=True)
@@ -157,3 +207,6 @@ class Trainer(object):
         if self.engine is not None:
             self.engine.close()
             self.engine = None
+        if self.cnn_engine is not None:
+            self.cnn_engine.close()
+            self.cnn_engine = None

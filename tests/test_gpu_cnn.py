@@ -204,3 +204,62 @@ def test_cnn_trains_on_synthetic_data():
     with torch.no_grad():
         acc = (model(x[:1024]).argmax(1) == y[:1024]).float().mean().item()
     assert acc > 0.8
+
+
+def test_native_cnn_step_matches_autograd_path():
+    """The C++ step executor (ops.cnn_engine) against the autograd Functions + FusedAdam: same
+    kernels, same data, dropout off -> same parameters after a few steps (atomic-order noise only)."""
+    import pytorch_distributed_mnist_b200 as pdm
+    from pytorch_distributed_mnist_b200.ops.cnn_engine import CnnEngine
+    torch.manual_seed(11)
+    a = pdm.CNN().cuda().eval()
+    b = pdm.CNN().cuda().eval()
+    b.load_state_dict(a.state_dict())
+    oa = pdm.FusedAdam(a.parameters(), lr=1e-3)
+    ob = pdm.FusedAdam(b.parameters(), lr=1e-3)
+    eng = CnnEngine(b, ob.flat, ob, ddp=None, max_batch=64)
+    g = torch.Generator().manual_seed(3)
+    for step in range(3):
+        x = torch.randint(0, 256, (64, 784), generator=g, dtype=torch.uint8).cuda()
+        y = torch.randint(0, 10, (64,), generator=g).cuda()
+        loss = F.cross_entropy(a(x), y)
+        oa.zero_grad()
+        loss.backward()
+        oa.step()
+        got = eng.train_step(x, y)
+        assert abs(got.item() - loss.item()) < 2e-3 * max(1.0, abs(loss.item())), (step, got.item(), loss.item())
+    for (n, p), (_, q) in zip(a.named_parameters(), b.named_parameters()):
+        rel = ((p - q).norm() / (p.norm() + 1e-12)).item()
+        assert rel < 2e-3, '{}: {}'.format(n, rel)
+    assert ob.step_count == 3
+    loss_sum, correct, samples = eng.read_metrics()
+    assert samples == 192 and 0 <= correct <= 192
+    logits = eng.eval_step(x, y, want_logits=True)
+    _rel(logits, a(x).detach(), 2e-2)
+    eng.close()
+
+
+def test_trainer_uses_native_cnn_engine(free_port):
+    import torch.distributed as dist
+    import pytorch_distributed_mnist_b200 as pdm
+    dist.init_process_group('gloo', init_method='tcp://127.0.0.1:{}'.format(free_port), world_size=1, rank=0)
+    try:
+        torch.manual_seed(0)
+        model = pdm.DistributedDataParallel(pdm.CNN().cuda(), device_ids=[0])
+        opt = pdm.FusedAdam(model.parameters(), lr=1e-3)
+        tl = pdm.MNISTDataLoader('nowhere', 128, 2, train=True, synthetic=True, size=4096)
+        vl = pdm.MNISTDataLoader('nowhere', 128, 2, train=False, synthetic=True, size=1024)
+        tr = pdm.Trainer(model, opt, tl, vl, torch.device('cuda', 0))
+        assert tr.cnn_engine is not None and tr.engine is None
+        first = None
+        for ep in range(2):
+            tl.set_sample_epoch(ep)
+            loss, acc = tr.train()
+            first = first if first is not None else loss.average
+        tloss, tacc = tr.evaluate()
+        assert loss.average < 0.7 * first and tacc.accuracy > 0.8
+        assert opt.step_count == 64
+        tr.close()
+        model.close()
+    finally:
+        dist.destroy_process_group()
