@@ -123,10 +123,12 @@ typedef struct pdm_net_step_args {
                                  kernel gather a shuffled batch itself from a dataset that is resident in
                                  device memory -- or in pinned, mapped host memory (zero-copy over PCIe). */
   int32_t flag_dependency;    /* 1: the caller can order this step after the previous one through sync[2] (a
-                                 count of finished CTAs) instead of grid completion, which would let the remote
-                                 stores of step n drain under step n+1.  Experimental: honoured only when the
-                                 process runs with PDM_NET_DEP=flag (it measured slower than the default on
-                                 B200).  Needs `sync` to be at least 3 words and done_before to be exact. */
+                                 count of finished CTAs) instead of grid completion; 2: this launch is counted in
+                                 sync[2] but still waits for its predecessor by grid completion (use for the first
+                                 step of a run, when uncounted work may precede it on the stream).  Used by default
+                                 in multi-GPU jobs, where it is faster (12.6 vs 17.8 us/step at 2 GPUs together
+                                 with the pulled LL exchange), not on one GPU (10.3 vs 8.7); PDM_NET_DEP=grid|flag
+                                 forces one.  Needs `sync` to be at least 3 words and done_before to be exact. */
   uint32_t done_before;       /* sum of pdm_net_planned_ctas() over all earlier steps issued on these sync words */
 } pdm_net_step_args;
 

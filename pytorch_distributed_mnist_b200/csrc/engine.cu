@@ -389,7 +389,7 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
         rc = pdm_comm_peers(e->comm, &a.peers, 1);
         if (rc != PDM_OK) break;
       }
-      a.flag_dependency = 1;
+      a.flag_dependency = b == 0 ? 2 : 1;   // first step of a run: ordered after whatever ran before by the grid dependency
       a.done_before = e->done_total;
       rc = pdm_net_train_step(&a, cs);
       if (rc == PDM_OK) e->done_total += (uint32_t)pdm_net_planned_ctas(n, ctas);
@@ -499,7 +499,7 @@ int pdm_engine_run_device(pdm_engine* e, const uint8_t* dev_images, const uint8_
       int rc = pdm_comm_peers(e->comm, &a.peers, 1);
       if (rc != PDM_OK) return rc;
     }
-    a.flag_dependency = 1;
+    a.flag_dependency = i == 0 ? 2 : 1;
     a.done_before = e->done_total;
     int rc = pdm_net_train_step(&a, st);
     if (rc != PDM_OK) return rc;
@@ -618,7 +618,7 @@ int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, 
       rc = pdm_comm_peers(e->comm, &a.peers, 1);
       if (rc != PDM_OK) return rc;
     }
-    a.flag_dependency = 1;
+    a.flag_dependency = b == 0 ? 2 : 1;
     a.done_before = e->done_total;
     rc = pdm_net_train_step(&a, cs);
     if (rc != PDM_OK) return rc;

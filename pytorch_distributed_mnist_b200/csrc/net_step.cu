@@ -81,10 +81,12 @@ struct KernelArgs {
   float* logits_out;
   long long* trace;   // optional [gridDim.x][8] clock64 stamps (bring-up / profiling aid)
   const int* row_index;   // optional [batch]: batch row r is row row_index[r] of x / y (in-kernel gather)
-  int flag_dep;           // 1: wait for the previous step through sync[2] instead of griddepcontrol.wait
+  int flag_dep;           // 1: bump sync[2] when a CTA is done (step-to-step flag dependency in use)
+  int flag_wait;          // 1: wait for the previous step through sync[2] instead of griddepcontrol.wait
   uint32_t done_before;   // value sync[2] reaches once every CTA of every earlier launch has finished
   int trigger_early;      // 1: release the next step's launch as soon as this grid is resident
   int poll_ns;            // back-off between polls of sync[2]
+  int ll_pull;            // 1: publish into our own outbox and read the peers' outboxes over NVLink
   OptConsts oc;
   pdm_peers peers;
 };
@@ -221,7 +223,7 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
   // CTAs have finished phase 2 (each bumps sync[2] after its last local store, release/acquire
   // at gpu scope), so remote traffic of step n drains under step n+1.
   if (MODE == 0) {
-    if (a.flag_dep) {
+    if (a.flag_wait) {
       if (tid == 0) {
         while ((int32_t)(ld_acquire_gpu(a.sync + 2) - a.done_before) < 0) {
           if (a.poll_ns > 0) __nanosleep(a.poll_ns);
@@ -492,14 +494,25 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
       // lanes' values, identically on every rank.
       const size_t par = (size_t)(seq & 1u) * W;
       const bool remote = valid && sub < W && sub != a.peers.rank;
-      if (remote) {
+      // push (default): write our value into slot `rank` of every peer's inbox, poll our own inbox.
+      // pull (PDM_NET_LL=pull): write it once into slot `rank` of OUR inbox and poll slot `sub` of
+      // peer `sub`'s inbox over NVLink: a round trip per poll instead of a one-way store, but the
+      // kernel retires with no remote stores in flight, so the next step does not wait for their
+      // acknowledgements.
+      if (a.ll_pull) {
+        if (valid && sub == a.peers.rank) {
+          uint64_t* dst = a.peers.inbox[a.peers.rank] + ((par + a.peers.rank) * kFlat4 + j) * 4;
+          ll_store2(dst, acc.x, acc.y, seq);
+          ll_store2(dst + 2, acc.z, acc.w, seq);
+        }
+      } else if (remote) {
         uint64_t* dst = a.peers.inbox[sub] + ((par + a.peers.rank) * kFlat4 + j) * 4;
         ll_store2(dst, acc.x, acc.y, seq);
         ll_store2(dst + 2, acc.z, acc.w, seq);
       }
       float4 q = (valid && sub == a.peers.rank) ? acc : make_float4(0.f, 0.f, 0.f, 0.f);
       if (remote) {
-        const uint64_t* src = a.peers.inbox[a.peers.rank] + ((par + sub) * kFlat4 + j) * 4;
+        const uint64_t* src = a.peers.inbox[a.ll_pull ? sub : a.peers.rank] + ((par + sub) * kFlat4 + j) * 4;
         bool ok0 = false, ok1 = false;
         uint64_t t0 = 0;
         uint32_t spins = 0;
@@ -753,16 +766,27 @@ extern "C" int pdm_net_train_step(const pdm_net_step_args* args, pdm_stream_t st
   ka.step_out = args->step_out;
   ka.row_index = args->row_index;
   {
-    // bring-up knobs: PDM_NET_DEP=grid|flag, PDM_NET_TRIGGER=barrier|start, PDM_NET_POLL_NS=<n>
-    // Measured on B200 (profiles/raw/step_sweep_dep.log): the flag dependency does not beat
-    // griddepcontrol.wait (10.3 vs 8.7 us/step on one GPU, 15.4 vs 14.8 on two), so it is opt-in.
-    static const int dep_flag = [] { const char* e = getenv("PDM_NET_DEP"); return (e && !strcmp(e, "flag")) ? 1 : 0; }();
+    // knobs: PDM_NET_DEP=grid|flag, PDM_NET_LL=push|pull, PDM_NET_TRIGGER=barrier|start, PDM_NET_POLL_NS=<n>.
+    // Measured on B200 (profiles/raw/step_sweep_dep.log, step_sweep_multi_ll_2.log), us/step at B = 512:
+    //   1 GPU : grid 8.7, flag 10.3                      -> grid
+    //   2 GPUs: push+grid 17.8, push+flag 16.0, pull+grid 15.3, pull+flag 12.6  -> pull + flag
+    // With peers, whatever waits for this grid's memory traffic to drain (grid completion, or the
+    // fence before the sync[2] bump) also waits for the acknowledgement of pushed remote stores;
+    // pulled data leaves nothing in flight.  Unset knobs therefore follow the world size.
+    static const int dep_env = [] { const char* e = getenv("PDM_NET_DEP"); return !e ? -1 : (!strcmp(e, "flag") ? 1 : 0); }();
+    static const int pull_env = [] { const char* e = getenv("PDM_NET_LL"); return !e ? -1 : (!strcmp(e, "pull") ? 1 : 0); }();
     static const int early = [] { const char* e = getenv("PDM_NET_TRIGGER"); return (e && !strcmp(e, "barrier")) ? 0 : 1; }();
     static const int poll = [] { const char* e = getenv("PDM_NET_POLL_NS"); return e && *e ? atoi(e) : 0; }();
+    const int dep_flag = dep_env >= 0 ? dep_env : (world > 1 ? 1 : 0);
+    // flag_dependency 1: count this launch's CTAs in sync[2] and wait for the earlier ones through it;
+    // 2: count, but wait with griddepcontrol.wait (first step of a run: whatever ran before on the
+    // stream may not have been counted)
     ka.flag_dep = (args->flag_dependency && dep_flag && launch_mode() == LAUNCH_PDL) ? 1 : 0;
+    ka.flag_wait = (ka.flag_dep && args->flag_dependency == 1) ? 1 : 0;
     ka.done_before = args->done_before;
-    ka.trigger_early = (ka.flag_dep && early) ? 1 : 0;
+    ka.trigger_early = (ka.flag_wait && early) ? 1 : 0;
     ka.poll_ns = poll;
+    ka.ll_pull = pull_env >= 0 ? pull_env : (world > 1 ? 1 : 0);
   }
   ka.oc = make_consts(h, world);
   ka.peers = args->peers;
