@@ -7,7 +7,7 @@
 //           DDP reducer            -> 4 bucket copies + ncclAllReduce      (K8-K10)
 //   ref:92  optimizer.step()       -> 8 _foreach launches                  (K11)
 //   ref:94-95 loss.item(), argmax/eq/sum/.item() -> 4 kernels + 2 host syncs (K12-K13)
-// ~25 launches and two syncs for 16 MFLOP.  Here: one cooperative launch.
+// ~25 launches and two syncs for 16 MFLOP.  Here: one launch.
 //
 // Shape of the kernel (B = local batch, G = CTAs, RT = rows per tile):
 //   phase 1  CTA c owns a contiguous slice of the batch.  Thread t < 196 owns
@@ -22,10 +22,11 @@
 //   phase 2  The 1963 float4 of the flat gradient are spread over all CTAs.
 //            Each thread sums the G partials in CTA order (deterministic),
 //            exchanges with the peers (LL protocol: 8-byte {value, flag}
-//            units pushed straight into every peer's inbox over NVLink,
-//            receiver polls its own memory), sums in rank order so every rank
-//            gets bit-identical parameters, scales by 1/world and applies
-//            Adam / SGD-momentum in registers.
+//            units over NVLink -- published in this rank's outbox and read
+//            by the peers, or pushed into the peers' inboxes; see the knob
+//            comment in pdm_net_train_step), sums in rank order so every
+//            rank gets bit-identical parameters, scales by 1/world and
+//            applies Adam / SGD-momentum in registers.
 // Metrics never leave the device unless asked: {loss*B, correct, B} are
 // accumulated into a device buffer, and optionally {mean loss, correct} of
 // this step is written to step_out (which may be mapped host memory).
