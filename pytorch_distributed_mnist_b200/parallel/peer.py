@@ -83,7 +83,11 @@ class PeerComm(object):
         devices = list(devices) if devices is not None else list(range(world))
         if world > _lib.PDM_MAX_RANKS or any(d >= n for d in devices):
             return False
-        for a in devices:
+        from . import topology
+        topo = topology.discover()
+        if topo.n == n and 'cuda-runtime' in topo.sources:
+            return topo.all_peer_access(devices)
+        for a in devices:               # discovery unavailable: ask the runtime directly
             for b in devices:
                 if a != b and not torch.cuda.can_device_access_peer(a, b):
                     return False

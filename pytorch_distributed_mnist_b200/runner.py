@@ -81,6 +81,9 @@ def _run(args):
         torch.cuda.set_device(device)
 
     print("rank: {}, device count: {}, workers:{}".format(rank, ngpus, args.workers))
+    if getattr(args, 'print_topology', False) and rank == 0:
+        from .parallel import topology
+        print(topology.discover().summary(range(args.world_size) if device.type == 'cuda' else None))
 
     model = build_model(getattr(args, 'arch', 'linear'), getattr(args, 'width', 1))
     if distributed_is_initialized():
