@@ -78,6 +78,9 @@ def build_parser():
                              'resident in HBM, gathered in-kernel; zerocopy = kernel gathers from pinned host memory; '
                              'auto = staged when the host has >= 12 cores per rank, else zerocopy')
     parser.add_argument('--checkpoint-dir', type=str, default=None, help='default: ./checkpoints (ref:264)')
+    parser.add_argument('--comm-timeout', type=float, default=30.0,
+                        help='seconds a peer-memory collective waits for a rank that does not show up before it '
+                             'aborts with the missing rank\'s number (the reference hangs until the NCCL watchdog)')
     parser.add_argument('--print-topology', action='store_true',
                         help='rank 0 prints what the bootstrap found out about the GPU interconnect '
                              '(peer access matrix, NVLink/NVSwitch links, multicast support)')

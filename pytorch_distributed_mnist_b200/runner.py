@@ -94,7 +94,8 @@ def _run(args):
             store = store_for_job(args.init_method, rank)
         model = DistributedDataParallel(
             model, device_ids=[device.index] if device.type == 'cuda' else None,
-            comm=getattr(args, 'comm', 'auto'), store=store)
+            comm=getattr(args, 'comm', 'auto'), store=store,
+            comm_timeout_s=float(getattr(args, 'comm_timeout', 30.0)))
 
     optimizer = build_optimizer(getattr(args, 'optimizer', 'adam'), model.parameters(), args)
 
