@@ -130,6 +130,9 @@ class CnnEngine(object):
         if seed is None:
             seed = int(torch.randint(0, 2 ** 62, (1,)).item())
         plan = self._plan()
+        if self.comm is not None:
+            for lo, hi in self._ranges:          # buckets >= 256 KB take the two-shot kernel: state is slice-wise
+                self.flat.mark_sharded(lo, hi, self.world)
         train = self.cnn.training
         _lib.check(self._lib.pdm_cnn_train_step(
             self._h, x.data_ptr(), _lib.dtype_code(x), y.data_ptr(), _lib.dtype_code(y), x.size(0),

@@ -26,11 +26,19 @@ from __future__ import annotations
 
 import ctypes
 import math
+import warnings
 
 import torch
 
 from .ops import _lib
 from .parallel.flat import FlatState, flat_of
+
+
+def _warn_if_stale(flat):
+    if getattr(flat, 'state_stale', False):
+        warnings.warn('optimizer state of buckets updated by the two-shot fused all-reduce is only current on the rank '
+                      'that owns each slice; call DistributedDataParallel.consolidate_optimizer_state() on every rank '
+                      'before state_dict() (runner.run does this before each checkpoint)', RuntimeWarning, stacklevel=3)
 
 
 class _FusedBase(torch.optim.Optimizer):
@@ -137,6 +145,7 @@ class FusedAdam(_FusedBase):
 
     # -- checkpoint compatibility -------------------------------------------
     def state_dict(self):
+        _warn_if_stale(self.flat)
         for p in self.flat.param_list:
             self.state[p]['step'] = self._step_tensor()
         sd = super().state_dict()
@@ -207,6 +216,7 @@ class FusedSGD(_FusedBase):
         flat.params.add_(grad, alpha=-g['lr'])
 
     def state_dict(self):
+        _warn_if_stale(self.flat)
         sd = super().state_dict()
         for st in sd['state'].values():
             for k, v in list(st.items()):

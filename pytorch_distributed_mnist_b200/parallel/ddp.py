@@ -238,6 +238,7 @@ class DistributedDataParallel(nn.Module):
             with torch.cuda.stream(cs):
                 if opt is not None:
                     h = opt.hyper(opt.step_count + 1)
+                    flat.mark_sharded(lo, hi, self.world)      # >= 256 KB: two-shot, state updated slice-wise
                     self.comm.allreduce_optim(flat.grads[lo:hi], flat.params[lo:hi], flat.exp_avg[lo:hi],
                                               flat.exp_avg_sq[lo:hi], h, stream=cs)
                 elif self.world > 1:
@@ -265,6 +266,12 @@ class DistributedDataParallel(nn.Module):
         not serialise the whole flat/symmetric buffer they are views of."""
         sd = super().state_dict(*args, **kwargs)
         return OrderedDict((k, v.detach().clone()) for k, v in sd.items())
+
+    def consolidate_optimizer_state(self):
+        """Collective (call on every rank): gather the optimizer-state slices that the two-shot
+        fused update keeps current only on their owning rank, so that ``optimizer.state_dict()``
+        is complete -- needed before a checkpoint is written.  No-op on the other paths."""
+        return self.flat.consolidate()
 
     def close(self):
         for h in self._hooks:

@@ -14,10 +14,22 @@ its ``.grad`` and its optimizer state are views into it.  Consequences:
 Layout rule: parameters in ``module.parameters()`` order, each starting on a
 4-float (16-byte) boundary; for ``Net`` this gives exactly the
 ``PDM_NET_FLAT`` layout of ``include/pdmnist.h`` (weight at 0, bias at 7840).
+
+Sharded optimizer state.  The two-shot form of the fused all-reduce + optimizer
+(``csrc/comm.cu``, buckets >= 256 KB) lets rank r update only slice r of a
+bucket: parameters are written to every replica, but ``exp_avg`` /
+``exp_avg_sq`` of a slice stay current only on the rank that owns it.  That is
+invisible while training (a rank only ever reads its own slice) but a
+checkpoint written by rank 0 (ref:249-254) needs all of it, so whoever launches
+such an update calls ``mark_sharded`` and ``consolidate`` gathers the slices
+before the state is read (``runner.run`` does this before every save).
 """
 from __future__ import annotations
 
 import torch
+
+# pdm_comm_allreduce_optim (algo = 0) switches to the two-shot kernel at this bucket size
+TWO_SHOT_MIN_BYTES = 256 * 1024
 
 
 def _round_up(x, m):
@@ -53,6 +65,8 @@ class FlatState(object):
             setattr(self, name, self.storage[i * self.section:i * self.section + self.numel])
         self.optimizer = None          # set by FusedOptimizer
         self.fused_applied = False     # a reducer already applied this step's update
+        self.sharded = {}              # (lo, hi) -> world: buckets whose optimizer state is updated slice-wise
+        self.state_stale = False       # a slice-wise update ran since the last consolidate()
         with torch.no_grad():
             for p, o in zip(params, self.offsets):
                 view = self.params[o:o + p.numel()].view(p.shape)
@@ -83,6 +97,55 @@ class FlatState(object):
         lo = self.offsets[first]
         hi = _round_up(self.offsets[last] + self.param_list[last].numel(), 4)
         return lo, hi
+
+
+    # -- sharded optimizer state (see the module docstring) ---------------------
+    @staticmethod
+    def slice_of(lo, hi, world, rank):
+        """Float range of bucket [lo, hi) that ``rank`` owns in the two-shot kernel: the bucket's
+        float4s are cut into ``world`` runs of ceil(n4 / world) (the last ones may be short or empty)."""
+        n4 = (hi - lo) // 4
+        per = (n4 + world - 1) // world
+        a = min(n4, per * rank)
+        b = min(n4, a + per)
+        return lo + 4 * a, lo + 4 * b
+
+    def mark_sharded(self, lo, hi, world):
+        """Record that the fused update of floats [lo, hi) runs slice-wise over ``world`` ranks."""
+        if world > 1 and 4 * (hi - lo) >= TWO_SHOT_MIN_BYTES:
+            self.sharded[(int(lo), int(hi))] = int(world)
+            self.state_stale = True
+
+    def consolidate(self, group=None):
+        """Collective: make ``exp_avg`` / ``exp_avg_sq`` complete on every rank.  Call on all ranks
+        (like ``ZeroRedundancyOptimizer.consolidate_state_dict``); a no-op when nothing is sharded."""
+        import torch.distributed as dist
+        if not self.sharded or not self.state_stale:
+            return 0
+        if not (dist.is_available() and dist.is_initialized()):
+            self.state_stale = False
+            return 0
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        via_host = self.exp_avg.is_cuda and dist.get_backend(group) != 'nccl'
+        moved = 0
+        with torch.no_grad():
+            for (lo, hi), w in sorted(self.sharded.items()):
+                if w != world:
+                    raise RuntimeError('bucket [{}, {}) was sharded over {} ranks, the group has {}'.format(lo, hi, w, world))
+                per = (((hi - lo) // 4) + world - 1) // world * 4
+                mine_lo, mine_hi = self.slice_of(lo, hi, world, rank)
+                for buf in (self.exp_avg, self.exp_avg_sq):
+                    send = torch.zeros(per, dtype=buf.dtype, device='cpu' if via_host else buf.device)
+                    send[:mine_hi - mine_lo].copy_(buf[mine_lo:mine_hi])
+                    parts = [torch.empty_like(send) for _ in range(world)]
+                    dist.all_gather(parts, send, group=group)
+                    for r in range(world):
+                        r_lo, r_hi = self.slice_of(lo, hi, world, r)
+                        if r != rank and r_hi > r_lo:
+                            buf[r_lo:r_hi].copy_(parts[r][:r_hi - r_lo])
+                            moved += r_hi - r_lo
+        self.state_stale = False
+        return moved
 
 
 def flat_of(params):

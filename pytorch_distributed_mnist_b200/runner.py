@@ -154,6 +154,9 @@ def _run(args):
             is_best = test_acc.accuracy > best_acc
             best_acc = max(test_acc.accuracy, best_acc)
 
+            # every rank: the two-shot fused update keeps optimizer-state slices on their owners
+            if hasattr(model, 'consolidate_optimizer_state'):
+                model.consolidate_optimizer_state()
             # only save checkpoints in the first gpu
             if args.rank == 0:
                 ckpt.save_checkpoint(ckpt.make_state(epoch, model, best_acc, optimizer), is_best, epoch, chk_dir)

@@ -180,3 +180,48 @@ def test_reference_checkpoint_resumes_here_and_ours_loads_in_stock(tmp_path, fre
     lin = torch.nn.Linear(784, 10)
     lin.load_state_dict({k.replace('module.fc.', ''): v for k, v in ours['state_dict'].items()})
     torch.optim.Adam(lin.parameters()).load_state_dict(ours['optimizer'])
+
+
+def _consolidate_worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+    from pytorch_distributed_mnist_b200.parallel.flat import FlatState
+    dist.init_process_group('gloo', init_method='tcp://127.0.0.1:{}'.format(port), world_size=world, rank=rank)
+    try:
+        torch.manual_seed(0)
+        # one bucket large enough for the two-shot kernel (>= 256 KB), one small, odd sizes on purpose
+        params = [torch.nn.Parameter(torch.zeros(70001)), torch.nn.Parameter(torch.zeros(33)), torch.nn.Parameter(torch.zeros(7))]
+        flat = FlatState(params)
+        lo, hi = flat.range_of(0, 0)
+        small = flat.range_of(1, 2)
+        truth_m = torch.arange(flat.numel, dtype=torch.float32) * 0.5
+        truth_v = torch.arange(flat.numel, dtype=torch.float32) + 3.0
+        # what the two-shot kernel leaves behind: only the owned slice of the big bucket is current
+        flat.exp_avg.fill_(-1.0)
+        flat.exp_avg_sq.fill_(-1.0)
+        a, b = FlatState.slice_of(lo, hi, world, rank)
+        flat.exp_avg[a:b] = truth_m[a:b]
+        flat.exp_avg_sq[a:b] = truth_v[a:b]
+        flat.exp_avg[small[0]:small[1]] = truth_m[small[0]:small[1]]       # small buckets: every rank updates all of it
+        flat.exp_avg_sq[small[0]:small[1]] = truth_v[small[0]:small[1]]
+        flat.mark_sharded(lo, hi, world)
+        flat.mark_sharded(small[0], small[1], world)                        # below the threshold: not recorded
+        assert list(flat.sharded) == [(lo, hi)] and flat.state_stale
+        moved = flat.consolidate()
+        assert moved == 2 * ((hi - lo) - (b - a)) and not flat.state_stale      # both moment buffers
+        assert torch.equal(flat.exp_avg, truth_m) and torch.equal(flat.exp_avg_sq, truth_v)
+        assert flat.consolidate() == 0                                      # nothing new since
+        # the slices tile the bucket exactly, for every world size up to 8
+        for w in range(1, 9):
+            cuts = [FlatState.slice_of(lo, hi, w, r) for r in range(w)]
+            assert cuts[0][0] == lo and cuts[-1][1] == hi and all(cuts[i][1] == cuts[i + 1][0] for i in range(w - 1))
+        torch.save(1, os.path.join(out_dir, 'ok{}'.format(rank)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_optimizer_state_is_consolidated(tmp_path, free_port):
+    """Two-shot fused updates keep exp_avg/exp_avg_sq slices on their owners; consolidate() must
+    rebuild the full state on every rank before rank 0 writes a checkpoint (ref:249-254)."""
+    world = 3
+    mp.spawn(_consolidate_worker, args=(world, free_port, str(tmp_path)), nprocs=world)
+    assert all(os.path.isfile(str(tmp_path / 'ok{}'.format(r))) for r in range(world))

@@ -195,6 +195,20 @@ def _cnn_worker(rank, world, port, native=False):
         for o in others:
             assert torch.equal(o, mine), 'replicas diverged in the bucketed fused path'
         assert o_opt.step_count == 4
+        # the fc bucket (4.7 MB) takes the two-shot kernel: Adam's moments are updated slice-wise by their
+        # owners and must be gathered before a checkpoint; afterwards every rank holds the same complete state
+        assert ours.flat.state_stale and len(ours.flat.sharded) >= 1
+        ours.consolidate_optimizer_state()
+        assert not ours.flat.state_stale
+        for buf in (ours.flat.exp_avg, ours.flat.exp_avg_sq):
+            mine = buf.clone()
+            others = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(others, mine)
+            for o in others:
+                assert torch.equal(o, mine), 'optimizer state differs across ranks after consolidation'
+        lo, hi = sorted(ours.flat.sharded)[0]
+        f_lo, f_hi = ours.flat.slice_of(lo, hi, world, (rank + 1) % world)       # a slice this rank does not own
+        assert (ours.flat.exp_avg_sq[f_lo:f_hi] > 0).float().mean().item() > 0.1, 'moments of foreign slices are still empty'
         ours.comm.check_status()
         if eng is not None:
             eng.close()
