@@ -10,6 +10,8 @@ Per size, three device-timed numbers (CUDA events on the launching stream, max o
   peer        our plain all-reduce kernel (auto: one-shot < 256 KB <= two-shot)
   peer+adam   our fused all-reduce + 1/W + Adam kernel              (what our reducer launches)
   nccl+adam   dist.all_reduce + div + torch.optim.Adam(foreach) step (the stock equivalent)
+  nvls(+adam) with --nvls: the experimental in-switch (multimem) kernel of parallel/nvls.py; checked
+              against the peer kernel's result first, skipped with a note if the device has no multicast
 Bus bandwidth = 2 (W-1)/W * bytes / time, the usual all-reduce convention.
 """
 import argparse
@@ -45,6 +47,7 @@ def main():
     ap.add_argument('--iters', type=int, default=200)
     ap.add_argument('--warmup', type=int, default=20)
     ap.add_argument('--out', default='')
+    ap.add_argument('--nvls', action='store_true', help='also time the experimental NVLS (multimem) kernel')
     a = ap.parse_args()
     rank, local, world = int(os.environ['RANK']), int(os.environ['LOCAL_RANK']), int(os.environ['WORLD_SIZE'])
     dev = torch.device('cuda', local)
@@ -57,6 +60,24 @@ def main():
     comm = PeerComm(rank, world, dev, data_bytes=nmax * 4 * 5 + 8192)
     g, out, p, m, v = (comm.data_tensor(nmax) for _ in range(5))
     g.normal_()
+    nv = None
+    if a.nvls:
+        from pytorch_distributed_mnist_b200.parallel.nvls import NvlsRegion
+        if NvlsRegion.supported(local):
+            nv = NvlsRegion(rank, world, dev, data_bytes=nmax * 4 * 5 + 8192)
+            ng, nout, np_, nm, nvv = (nv.data_tensor(nmax) for _ in range(5))
+            ng.copy_(g)
+            # numerics first: in-switch sum vs the rank-ordered P2P sum (fp32, order may differ)
+            k = 1 << 20
+            comm.allreduce(g[:k], out[:k], average=True)
+            nv.allreduce(ng[:k], nout[:k], average=True)
+            torch.cuda.synchronize(dev)
+            err = (out[:k] - nout[:k]).abs().max().item()
+            if rank == 0:
+                print('nvls vs peer all-reduce: max abs diff {:.3e}'.format(err), flush=True)
+            assert err < 1e-5, 'NVLS all-reduce disagrees with the P2P kernel'
+        elif rank == 0:
+            print('nvls: device reports no multicast support, skipped', flush=True)
     rows = []
     for nbytes in sizes:
         n = nbytes // 4 // 4 * 4
@@ -81,18 +102,31 @@ def main():
         def peer_adam():
             comm.allreduce_optim(g[:n], p[:n], m[:n], v[:n], h)
 
+        def nvls_plain():
+            nv.allreduce(ng[:n], nout[:n], average=True)
+
+        def nvls_adam():
+            nv.allreduce_optim(ng[:n], np_[:n], nm[:n], nvv[:n], h)
+
         row = {'bytes': n * 4, 'world': world}
-        for name, fn in (('nccl', nccl), ('peer', peer), ('nccl_adam', nccl_adam), ('peer_adam', peer_adam)):
+        kinds = [('nccl', nccl), ('peer', peer), ('nccl_adam', nccl_adam), ('peer_adam', peer_adam)]
+        if nv is not None:
+            kinds += [('nvls', nvls_plain), ('nvls_adam', nvls_adam)]
+        for name, fn in kinds:
             us = timed(fn, iters, a.warmup, dev)
             row[name + '_us'] = round(us, 2)
             row[name + '_busbw_gbs'] = round(2 * (world - 1) / world * n * 4 / (us * 1e-6) / 1e9, 2)
         comm.check_status()
+        if nv is not None:
+            nv.check_status()
         rows.append(row)
         if rank == 0:
             print(json.dumps(row), flush=True)
     if rank == 0 and a.out:
         with open(a.out, 'w') as f:
             json.dump(rows, f, indent=1)
+    if nv is not None:
+        nv.close()
     comm.close()
     dist.destroy_process_group()
 

@@ -326,6 +326,33 @@ int pdm_comm_allreduce_optim(pdm_comm* c, size_t grad_off, size_t out_off, size_
 int pdm_comm_destroy(pdm_comm* c);
 
 /* ------------------------------------------------------------------------
+ * NVLS (multicast / multimem) region (nvls.cu).  EXPERIMENTAL: compiled, not yet
+ * run on hardware in round 1; nothing uses it unless asked (parallel/nvls.py).
+ * A symmetric region of VMM memory bound to a multicast object, so that
+ * `multimem.ld_reduce` sums an address over all replicas inside the NVSwitch and
+ * `multimem.st` writes all replicas with one store.  Bootstrap, in order:
+ *   every rank : pdm_nvls_create
+ *   rank 0     : pdm_nvls_export_fd, descriptor sent to the others (SCM_RIGHTS)
+ *   others     : pdm_nvls_import_fd
+ *   every rank : pdm_nvls_add_device, host barrier, pdm_nvls_bind, host barrier
+ * pdm_nvls_allreduce_optim has the contract of the two-shot
+ * pdm_comm_allreduce_optim; offsets are bytes into pdm_nvls_data(). */
+typedef struct pdm_nvls pdm_nvls;
+int pdm_nvls_supported(int device);                  /* 1 yes, 0 no, <0 error */
+int pdm_nvls_create(pdm_nvls** out, int rank, int world, int device, size_t data_bytes);
+int pdm_nvls_export_fd(pdm_nvls* nv, int* fd);
+int pdm_nvls_import_fd(pdm_nvls* nv, int fd);
+int pdm_nvls_add_device(pdm_nvls* nv);
+int pdm_nvls_bind(pdm_nvls* nv);
+void* pdm_nvls_data(pdm_nvls* nv);
+size_t pdm_nvls_data_bytes(pdm_nvls* nv);
+void pdm_nvls_set_timeout(pdm_nvls* nv, double seconds);
+int pdm_nvls_status(pdm_nvls* nv, int* status);
+int pdm_nvls_allreduce_optim(pdm_nvls* nv, size_t grad_off, size_t out_off, size_t m_off, size_t v_off,
+                             size_t n_floats, const pdm_hyper* hyper, float grad_scale, pdm_stream_t stream);
+int pdm_nvls_destroy(pdm_nvls* nv);
+
+/* ------------------------------------------------------------------------
  * TCP key-value rendezvous store (store.cu; host code only).  The role of the
  * c10d TCPStore behind the reference's tcp:// init method (ref:167-168,
  * ref:323-327) as far as this framework needs it: publishing the

@@ -281,3 +281,42 @@ def test_dead_peer_is_reported_not_hung(free_port):
     """a rank that never reaches a collective must produce a diagnosable error
     on its peers (bounded device-side wait + status word), not a hung GPU."""
     mp.spawn(_timeout_worker, args=(2, free_port), nprocs=2)
+
+
+def _nvls_worker(rank, world, port):
+    from pytorch_distributed_mnist_b200.ops import _lib
+    from pytorch_distributed_mnist_b200.parallel.nvls import NvlsRegion
+    _init(rank, world, port)
+    try:
+        dev = torch.device('cuda', rank)
+        n = 1 << 18
+        nv = NvlsRegion(rank, world, dev, data_bytes=n * 4 * 5 + 8192)
+        g, out, p, m, v = (nv.data_tensor(n) for _ in range(5))
+        g.copy_(_rand(300 + rank, n))
+        torch.cuda.synchronize()
+        dist.barrier()
+        nv.allreduce(g, out, average=True)
+        torch.cuda.synchronize()
+        want = sum(_rand(300 + r, n) for r in range(world)) / world
+        torch.testing.assert_close(out.cpu(), want, rtol=1e-5, atol=1e-6)
+        # fused Adam: every replica must end with the same parameters as torch.optim.Adam on the mean gradient
+        p.copy_(_rand(7, n))
+        ref_p = _rand(7, n).to(dev).requires_grad_(True)
+        ref_p.grad = want.to(dev)
+        torch.optim.Adam([ref_p], lr=1e-3).step()
+        h = _lib.Hyper(opt=_lib.PDM_OPT_ADAM, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0, step=1)
+        torch.cuda.synchronize()
+        dist.barrier()
+        nv.allreduce_optim(g, p, m, v, h)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(p, ref_p.detach(), rtol=1e-5, atol=1e-6)
+        nv.check_status()
+        nv.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(os.environ.get('PDM_TEST_NVLS', '') in ('', '0'),
+                    reason='experimental NVLS path: opt in with PDM_TEST_NVLS=1 (not yet validated on hardware)')
+def test_nvls_allreduce_optim(free_port):
+    mp.spawn(_nvls_worker, args=(_world(), free_port), nprocs=_world())
