@@ -82,6 +82,8 @@ class Topology(object):
         devices = list(range(self.n)) if devices is None else list(devices)
         out = ['interconnect: {} ({} device{}; probes: {})'.format(
             self.kind(devices), len(devices), '' if len(devices) == 1 else 's', ', '.join(self.sources) or 'none')]
+        if not devices:
+            return out[0] + ' -- no CUDA devices: gradients go through torch.distributed (--comm group)'
         head = '      ' + ' '.join('GPU{:<3d}'.format(d) for d in devices)
         out.append(head)
         for a in devices:
