@@ -323,11 +323,6 @@ EncodeFn get_encode() {
 }
 
 // 2-D fp32 row-major matrix [rows][cols] with leading dimension ld (elements); box = {32 cols, box_rows}.
-int env_int(const char* name, int dflt) {
-  const char* e = getenv(name);
-  return (e && *e) ? atoi(e) : dflt;
-}
-
 int make_map(CUtensorMap* map, const float* base, long long rows, long long cols, long long ld, int box_rows, int mn_major) {
   EncodeFn enc = get_encode();
   PDM_REQUIRE(enc != nullptr, PDM_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
@@ -338,8 +333,7 @@ int make_map(CUtensorMap* map, const float* base, long long rows, long long cols
   cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1u, 1u};
   // MN-major tf32: 128 B swizzle with 32 B atomicity (the only layout UMMA accepts for it)
-  static const int mn_swizzle = env_int("PDM_GEMM_MN_TMA_SWIZZLE", (int)CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
-  const CUtensorMapSwizzle swz = mn_major ? (CUtensorMapSwizzle)mn_swizzle : CU_TENSOR_MAP_SWIZZLE_128B;
+  const CUtensorMapSwizzle swz = mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -395,13 +389,10 @@ extern "C" int pdm_gemm_tf32(const pdm_gemm_args* g, pdm_stream_t stream) {
   p.tiles_m = (g->M + kBlockM - 1) / kBlockM;
   p.tiles_n = (g->N + block_n - 1) / block_n;
   p.splits = splits;
-  // MN-major descriptor fields (overridable for bring-up experiments)
-  static const int mn_layout = env_int("PDM_GEMM_MN_LAYOUT", 1);      // 1 = SWIZZLE_128B_BASE32B
-  static const int mn_sbo = env_int("PDM_GEMM_MN_SBO", 512);          // 4 k-rows x 128 B
-  static const int mn_lbo = env_int("PDM_GEMM_MN_LBO", (int)kAtomBytes);
-  p.mn_layout = (uint32_t)mn_layout;
-  p.mn_sbo = (uint32_t)mn_sbo;
-  p.mn_lbo = (uint32_t)mn_lbo;
+  // MN-major descriptor fields: found by experiment on B200, the only combination UMMA accepts for tf32
+  p.mn_layout = 1u;                    // SWIZZLE_128B_BASE32B
+  p.mn_sbo = 512u;                     // 4 k-rows x 128 B
+  p.mn_lbo = (uint32_t)kAtomBytes;
 
   CUtensorMap ma, mb;
   int rc = make_map(&ma, g->a, g->a_rows, g->a_cols, g->lda, p.a_mn ? kBlockK : kBlockM, p.a_mn);
