@@ -2,7 +2,7 @@
 //
 // STATUS: written and compiled for sm_100a in round 1 but NOT yet run on hardware (the round's
 // GPU budget was spent before it existed).  Nothing uses it by default: it is reached only through
-// parallel/nvls.py (PDM_COMM_NVLS=1 or an explicit NvlsRegion), and the P2P two-shot kernel in
+// parallel/nvls.py (an explicit NvlsRegion: benchmarks/allreduce_sweep.py --nvls), and the P2P two-shot kernel in
 // comm.cu remains the large-bucket path.  Treat every statement below as the design, not a result.
 //
 // What it replaces: for large buckets the reference's ncclAllReduce uses NVLS when the fabric has

@@ -96,11 +96,6 @@ def _d11(fn):
     fn.argtypes = [c_void_p]
 
 
-def requested():
-    """True when the user asked for the NVLS path (``PDM_COMM_NVLS=1``)."""
-    return os.environ.get('PDM_COMM_NVLS', '') not in ('', '0')
-
-
 def _wait_count(store, key, target, timeout_s):
     store.add(key, 1)
     t0 = time.time()
