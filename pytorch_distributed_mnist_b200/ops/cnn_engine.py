@@ -5,6 +5,12 @@ all-reduce + optimizer are all issued from C++ (bucket 0 overlaps the convolutio
 side stream).  Gradients land directly in the model's ``FlatState``; autograd is not involved.
 The autograd Functions in ``ops/cnn_ops.py`` remain the general path (custom losses, hooks,
 ``no_sync``); this engine is what ``Trainer`` uses for the stock training loop.
+
+Parity: one ``train_step`` is the body of the reference's loop (ref:84-95: H2D'd batch ->
+``model(data)`` -> ``cross_entropy`` -> ``zero_grad``/``backward`` (DDP reducer) ->
+``optimizer.step`` -> ``loss.item()`` / ``Accuracy.update``) for the CNN extension of
+BASELINE.json; ``eval_step`` is ref:106-114.  Metrics stay on the device until
+``read_metrics`` (one sync per epoch instead of two per step).
 """
 from __future__ import annotations
 

@@ -13,6 +13,12 @@ copies).  Internal contract between adjacent Functions: the gradient handed to `
 ``Conv1Fn`` is already multiplied by that layer's ReLU mask (the producer fuses it), which is
 idempotent, so each Function is still a correct autograd node on its own.
 
+Parity: the reference has no CNN; the layer list is the PyTorch-examples MNIST net
+that BASELINE.json's configs 2-4 name.  Each Function replaces the cuDNN / cuBLAS /
+ATen call the stock module would make for that layer (the "stock" arm of
+``benchmarks/bench_cnn.py``); numerics are checked against those stock ops in
+``tests/test_gpu_cnn.py``.
+
 The module's parameters stay in PyTorch layout (checkpoints are unchanged); conv2's weight is
 re-laid out for the GEMM by a tiny kernel each step.
 """

@@ -4,6 +4,10 @@
 needs and exposes ``train_step`` / ``eval_step`` on caller-provided device
 tensors.  The trainer's hot loop uses the native engine instead (no Python per
 step); this class is the building block for tests, notebooks and custom loops.
+
+Parity: ``train_step`` = ref:84-95 for one batch (SURVEY K1-K13 in one launch), ``eval_step`` =
+ref:106-114 (forward, loss and top-1 only), ``forward`` = ref:126.  The hyper-parameter structs
+mirror ``torch.optim.Adam`` (ref:191) and the SGD-momentum variant BASELINE.json asks for.
 """
 from __future__ import annotations
 

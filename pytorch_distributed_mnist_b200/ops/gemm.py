@@ -4,6 +4,9 @@
 row-major fp32 CUDA matrix used as stored (``[MN, K]``, K-major) or transposed
 (``[K, MN]``, MN-major) -- no transposed copies are made.  ``conv3x3_*`` are the
 implicit-GEMM modes over NHWC activations (see the .cu header for the shifted-row trick).
+
+Parity: stands where the reference stack calls cuBLAS SGEMM (``nn.Linear``) and,
+for the CNN extension, cuDNN convolution forward / dgrad / wgrad.
 """
 from __future__ import annotations
 
