@@ -28,6 +28,14 @@ def _fd_worker(rank, world, port, out_dir):
         with open(os.path.join(out_dir, 'got{}'.format(rank)), 'wb') as f:
             f.write(data)
     nvls._wait_count(store, 'pdm/test/done', world, 30.0)
+    # rank 0 hosts the store: it must outlive the other ranks' last poll
+    if rank == 0:
+        import time
+        t0 = time.time()
+        while int(store.add('pdm/test/left', 0)) < world - 1 and time.time() - t0 < 30:
+            time.sleep(0.01)
+    else:
+        store.add('pdm/test/left', 1)
 
 
 def test_descriptor_reaches_every_rank(tmp_path, free_port):
