@@ -42,6 +42,20 @@ def save_checkpoint(state, is_best, epoch, chk_dir=CHECKPOINT_DIR):
     return filename
 
 
+def latest_checkpoint(chk_dir=CHECKPOINT_DIR):
+    """Path of ``checkpoint_{epoch}.pth.tar`` with the highest epoch in ``chk_dir``, or None.
+    Used by ``--resume auto``: the reference's recovery story is "rerun with --resume PATH"
+    (README:50-52); this saves looking the path up after a crash."""
+    import re
+    best, best_epoch = None, -1
+    if os.path.isdir(chk_dir):
+        for name in os.listdir(chk_dir):
+            m = re.fullmatch(r'checkpoint_(\d+)\.pth\.tar', name)
+            if m and int(m.group(1)) > best_epoch:
+                best, best_epoch = os.path.join(chk_dir, name), int(m.group(1))
+    return best
+
+
 def load_checkpoint(path, map_location=None):
     """``torch.load`` with the safe (weights_only) default; reference
     checkpoints hold only tensors and primitives so this needs no override."""

@@ -38,7 +38,8 @@ def build_parser():
     parser.add_argument('--wd', '--weight-decay', default=1e-4, type=float, metavar='W',
                         help='weight decay (default: 1e-4; used by --optimizer sgd)', dest='weight_decay')
     parser.add_argument('--resume', default='', type=str, metavar='PATH',
-                        help='path to latest checkpoint (default: none)')
+                        help='path to latest checkpoint (default: none); "auto" = newest checkpoint_N.pth.tar in the '
+                             'checkpoint directory')
     parser.add_argument('-e', '--evaluate', dest='evaluate', action='store_true',
                         help='evaluate model on validation set')
     parser.add_argument('--backend', type=str, default='nccl', help='Name of the backend to use.')

@@ -99,7 +99,10 @@ def _run(args):
 
     optimizer = build_optimizer(getattr(args, 'optimizer', 'adam'), model.parameters(), args)
 
-    # optionally resume from a checkpoint
+    # optionally resume from a checkpoint ('auto' = the newest one in the checkpoint directory)
+    if args.resume == 'auto':
+        found = ckpt.latest_checkpoint(getattr(args, 'checkpoint_dir', None) or ckpt.CHECKPOINT_DIR)
+        args.resume = found if found is not None else 'auto'
     if args.resume:
         if os.path.isfile(args.resume):
             print("=> loading checkpoint '{}'".format(args.resume))

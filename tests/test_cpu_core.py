@@ -224,3 +224,13 @@ def test_native_library_builds_and_exports():
         assert hasattr(lib, sym)
     if not torch.cuda.is_available():
         assert lib.pdm_device_ok(0) == 0
+
+
+def test_resume_auto_picks_newest_checkpoint(tmp_path):
+    from pytorch_distributed_mnist_b200 import checkpoint as ckpt
+    assert ckpt.latest_checkpoint(str(tmp_path / 'missing')) is None
+    assert ckpt.latest_checkpoint(str(tmp_path)) is None
+    for name in ('checkpoint_2.pth.tar', 'checkpoint_10.pth.tar', 'checkpoint_9.pth.tar', 'model_best.pth.tar',
+                 'checkpoint_11.pth.tar.tmp'):
+        (tmp_path / name).write_bytes(b'x')
+    assert ckpt.latest_checkpoint(str(tmp_path)) == str(tmp_path / 'checkpoint_10.pth.tar')
