@@ -187,6 +187,19 @@ class DistributedDataParallel(nn.Module):
         return self.module(*inputs, **kwargs)
 
     def _arm(self):
+        # Stock DDP refuses to start an iteration when the previous one did not finish its reduction
+        # ("Expected to have finished reduction in the prior iteration"): a parameter that received no
+        # gradient leaves its bucket -- and every later one -- unreduced, and the ranks drift apart.
+        started = any(p != len(bk['params']) for p, bk in zip(self._pending, self.buckets))
+        if started and self._next_launch < len(self.buckets):
+            missing = [i for b in range(self._next_launch, len(self.buckets)) for i in self.buckets[b]['params']
+                       if self._pending[b] > 0]
+            raise RuntimeError(
+                'DistributedDataParallel: the previous backward pass did not produce gradients for every parameter '
+                '(buckets {}..{} were never reduced; parameters without a gradient are among indices {}). Every '
+                'parameter must take part in the loss (there is no find_unused_parameters mode), or wrap the '
+                'extra forward passes in no_sync() / torch.no_grad().'.format(
+                    self._next_launch, len(self.buckets) - 1, missing[:8]))
         self._pending = [len(bk['params']) for bk in self.buckets]
         self._ready = [False] * len(self.buckets)
         self._next_launch = 0

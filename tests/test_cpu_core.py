@@ -234,3 +234,29 @@ def test_resume_auto_picks_newest_checkpoint(tmp_path):
                  'checkpoint_11.pth.tar.tmp'):
         (tmp_path / name).write_bytes(b'x')
     assert ckpt.latest_checkpoint(str(tmp_path)) == str(tmp_path / 'checkpoint_10.pth.tar')
+
+
+def test_ddp_reports_parameters_without_gradient():
+    """A parameter that never gets a gradient leaves its bucket unreduced; like stock DDP this must
+    be an error at the next forward, not silent divergence."""
+    import pytorch_distributed_mnist_b200 as pdm
+
+    class TwoHeads(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.a = torch.nn.Linear(4, 3)
+            self.b = torch.nn.Linear(4, 3)
+
+        def forward(self, x, use_b=True):
+            return self.a(x) + (self.b(x) if use_b else 0)
+
+    model = pdm.DistributedDataParallel(TwoHeads())
+    opt = pdm.FusedSGD(model.parameters(), lr=0.1)
+    x = torch.randn(5, 4)
+    model(x).sum().backward()          # complete iteration
+    opt.step()
+    model(x).sum().backward()          # two forwards in a row are fine when each backward completes
+    opt.step()
+    model(x, use_b=False).sum().backward()      # head b gets no gradient
+    with pytest.raises(RuntimeError, match='did not produce gradients for every parameter'):
+        model(x)
