@@ -117,6 +117,7 @@ class DistributedDataParallel(nn.Module):
         self.rank = dist.get_rank(process_group) if dist.is_initialized() else 0
         self.fuse_optimizer = fuse_optimizer
         self.broadcast_buffers = broadcast_buffers
+        self._process_group = process_group
 
         # -- communicator ---------------------------------------------------
         numel = sum((p.numel() + 3) // 4 * 4 for p in params)
@@ -184,7 +185,29 @@ class DistributedDataParallel(nn.Module):
     def forward(self, *inputs, **kwargs):
         if torch.is_grad_enabled() and self.require_backward_grad_sync:
             self._arm()
+            self._sync_buffers()
         return self.module(*inputs, **kwargs)
+
+    def _sync_buffers(self):
+        """Stock DDP re-broadcasts module buffers (BatchNorm statistics, ...) from rank 0 at the start
+        of every training forward (``broadcast_buffers=True``, SURVEY 2.5: a no-op for ``Net`` and the
+        CNN, which have none).  Buffers are few and small: one flattened broadcast per dtype."""
+        if not self.broadcast_buffers or self.world == 1:
+            return
+        bufs = [b for b in self.module.buffers() if b is not None and b.numel() > 0]
+        if not bufs:
+            return
+        by_dtype = {}
+        for b in bufs:
+            by_dtype.setdefault(b.dtype, []).append(b)
+        with torch.no_grad():
+            for group in by_dtype.values():
+                flat = torch.cat([b.reshape(-1) for b in group])
+                dist.broadcast(flat, 0, group=self._process_group)
+                off = 0
+                for b in group:
+                    b.copy_(flat[off:off + b.numel()].view_as(b))
+                    off += b.numel()
 
     def _arm(self):
         # Stock DDP refuses to start an iteration when the previous one did not finish its reduction
