@@ -104,8 +104,17 @@ class DistributedDataParallel(nn.Module):
 
     def __init__(self, module, device_ids=None, output_device=None, broadcast_buffers=True,
                  bucket_cap_mb=DEFAULT_BUCKET_CAP_MB, comm='auto', fuse_optimizer=True,
-                 comm_timeout_s=30.0, process_group=None, store=None):
+                 comm_timeout_s=30.0, process_group=None, store=None, find_unused_parameters=False,
+                 gradient_as_bucket_view=True, static_graph=False):
         super().__init__()
+        # accepted for drop-in compatibility with torch's constructor (ref:188-189 passes only device_ids)
+        if find_unused_parameters:
+            raise NotImplementedError('find_unused_parameters=True is not supported: gradients are produced straight '
+                                      'into bucket memory and every parameter must receive one (see _arm)')
+        if not gradient_as_bucket_view:
+            raise NotImplementedError('gradients are always views of the flat bucket memory here '
+                                      '(gradient_as_bucket_view=False would add the copies this design removes)')
+        del static_graph        # the bucket schedule is static by construction
         self.module = module
         params = [p for p in module.parameters() if p.requires_grad]
         if not params:
