@@ -106,3 +106,24 @@ def test_cli_flag():
     from pytorch_distributed_mnist_b200.cli import build_parser
     assert build_parser().parse_args(['--print-topology']).print_topology is True
     assert build_parser().parse_args([]).print_topology is False
+
+
+def test_peer_comm_supported_uses_discovery(monkeypatch):
+    import torch
+    from pytorch_distributed_mnist_b200.ops import _lib
+    from pytorch_distributed_mnist_b200.parallel import peer
+    topo = T.discover(probes=(('cuda-runtime', _runtime(4, blocked=[(1, 2)])),))
+    topo.sources = ['cuda-runtime']
+    monkeypatch.setattr(torch.cuda, 'is_available', lambda: True)
+    monkeypatch.setattr(torch.cuda, 'device_count', lambda: 4)
+    monkeypatch.setattr(_lib, 'available', lambda: True)
+    monkeypatch.setattr(T, 'discover', lambda *a, **k: topo)
+    assert not peer.PeerComm.supported(4)                    # GPUs 1 and 2 cannot map each other
+    assert peer.PeerComm.supported(2, devices=[0, 3])
+    assert not peer.PeerComm.supported(8)                    # more ranks than devices
+    # discovery unavailable -> falls back to asking the runtime pair by pair
+    empty = T.Topology(0)
+    monkeypatch.setattr(T, 'discover', lambda *a, **k: empty)
+    asked = []
+    monkeypatch.setattr(torch.cuda, 'can_device_access_peer', lambda a, b: asked.append((a, b)) or True)
+    assert peer.PeerComm.supported(2) and (0, 1) in asked
