@@ -126,29 +126,43 @@ __global__ void __launch_bounds__(kThreadsNv) nvls_reduce_optim_kernel(const __g
   uint8_t* data_uc = A.uc + kFlagBytes;
   uint8_t* data_mc = A.mc + kFlagBytes;
   const bool has_state = A.k.opt != PDM_OPT_NONE;
-  const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
-    float4 g;
-    const float4* src = reinterpret_cast<const float4*>(data_mc + A.grad_off) + i;
-    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
-                 : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w) : "l"(src) : "memory");
-    float4 p4 = make_float4(0.f, 0.f, 0.f, 0.f), m4 = p4, v4 = p4;
-    if (has_state) {
-      p4 = reinterpret_cast<const float4*>(data_uc + A.out_off)[i];
-      m4 = reinterpret_cast<const float4*>(data_uc + A.m_off)[i];
-      if (A.k.opt == PDM_OPT_ADAM) v4 = reinterpret_cast<const float4*>(data_uc + A.v_off)[i];
+  // four independent in-switch reductions in flight per thread (one ld_reduce is a full NVLink round trip)
+  constexpr int kUnroll = 4;
+  const size_t chunk = (size_t)blockDim.x * kUnroll;
+  for (size_t base = lo + (size_t)blockIdx.x * chunk + threadIdx.x; base < hi; base += (size_t)gridDim.x * chunk) {
+    float4 g[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const size_t i = base + (size_t)u * blockDim.x;
+      g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (i < hi) {
+        const float4* src = reinterpret_cast<const float4*>(data_mc + A.grad_off) + i;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(g[u].x), "=f"(g[u].y), "=f"(g[u].z), "=f"(g[u].w) : "l"(src) : "memory");
+      }
     }
-    upd_n(A.k, g.x, p4.x, m4.x, v4.x);
-    upd_n(A.k, g.y, p4.y, m4.y, v4.y);
-    upd_n(A.k, g.z, p4.z, m4.z, v4.z);
-    upd_n(A.k, g.w, p4.w, m4.w, v4.w);
-    if (has_state) {
-      reinterpret_cast<float4*>(data_uc + A.m_off)[i] = m4;
-      if (A.k.opt == PDM_OPT_ADAM) reinterpret_cast<float4*>(data_uc + A.v_off)[i] = v4;
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const size_t i = base + (size_t)u * blockDim.x;
+      if (i >= hi) continue;
+      float4 p4 = make_float4(0.f, 0.f, 0.f, 0.f), m4 = p4, v4 = p4;
+      if (has_state) {
+        p4 = reinterpret_cast<const float4*>(data_uc + A.out_off)[i];
+        m4 = reinterpret_cast<const float4*>(data_uc + A.m_off)[i];
+        if (A.k.opt == PDM_OPT_ADAM) v4 = reinterpret_cast<const float4*>(data_uc + A.v_off)[i];
+      }
+      upd_n(A.k, g[u].x, p4.x, m4.x, v4.x);
+      upd_n(A.k, g[u].y, p4.y, m4.y, v4.y);
+      upd_n(A.k, g[u].z, p4.z, m4.z, v4.z);
+      upd_n(A.k, g[u].w, p4.w, m4.w, v4.w);
+      if (has_state) {
+        reinterpret_cast<float4*>(data_uc + A.m_off)[i] = m4;
+        if (A.k.opt == PDM_OPT_ADAM) reinterpret_cast<float4*>(data_uc + A.v_off)[i] = v4;
+      }
+      float4* dst = reinterpret_cast<float4*>(data_mc + A.out_off) + i;   // one store, every replica
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                   ::"l"(dst), "f"(p4.x), "f"(p4.y), "f"(p4.z), "f"(p4.w) : "memory");
     }
-    float4* dst = reinterpret_cast<float4*>(data_mc + A.out_off) + i;   // one store, every replica
-    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
-                 ::"l"(dst), "f"(p4.x), "f"(p4.y), "f"(p4.z), "f"(p4.w) : "memory");
   }
   // 2) nobody leaves before every rank's block b has issued its stores (release/acquire at system scope)
   mc_block_barrier(A, (2u * A.epoch + 2u) * W);
