@@ -77,12 +77,45 @@ def fmt(v, unit):
     return '{:.1f}'.format(x) if abs(x) < 1e5 else '{:.3g}'.format(x)
 
 
+def hot_instructions(path, kernel_regex, top):
+    """Top SASS instructions by warp-stall samples of the first matching launch (source page)."""
+    out = subprocess.run(['ncu', '-i', path, '--page', 'source', '--csv', '--kernel-name', 'regex:' + kernel_regex,
+                          '--launch-count', '1'], capture_output=True, text=True)
+    if out.returncode != 0:
+        return []
+    rows = list(csv.reader(io.StringIO(out.stdout)))
+    hdr = next((i for i, r in enumerate(rows) if r and r[0] == 'Address'), None)
+    if hdr is None:
+        return []
+    head = rows[hdr]
+    try:
+        i_src, i_smp = head.index('Source'), head.index('# Samples')
+    except ValueError:
+        return []
+    inst, seen = [], set()
+    for k, r in enumerate(rows[hdr + 1:]):
+        if len(r) <= i_smp or r[0] == 'Address' or not r[0].startswith('0x') or r[0] in seen:
+            continue
+        seen.add(r[0])       # the page can list the same code twice (one block per view)
+        try:
+            inst.append((int(r[i_smp]), k, r[i_src].strip()))
+        except ValueError:
+            pass
+    total = sum(n for n, _, _ in inst) or 1
+    lines = ['', 'Hottest SASS instructions of the first matching launch (warp-stall samples, {} total):'.format(total), '',
+             '| samples | share | instruction # | SASS |', '|---|---|---|---|']
+    for n, k, src in sorted(inst, reverse=True)[:top]:
+        lines.append('| {} | {:.1f} % | {} | `{}` |'.format(n, 100.0 * n / total, k, src.replace('|', '\\|')))
+    return lines
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('report')
     ap.add_argument('--kernel', default='.', help='regex on the kernel name')
     ap.add_argument('--out', default='')
     ap.add_argument('--title', default='')
+    ap.add_argument('--hot', type=int, default=12, help='how many hottest SASS instructions to list (0 = none)')
     a = ap.parse_args()
     head, units, data = read_raw(a.report)
     k_name, k_grid, k_block = col_index(head, 'Kernel Name'), col_index(head, 'Grid Size'), col_index(head, 'Block Size')
@@ -121,6 +154,8 @@ def main():
         tot = sum(v for v, _ in st) or 1.0
         stalls_out.append('* launch {}: '.format(r) + ', '.join('{} {:.0f} %'.format(n, 100 * v / tot) for v, n in st[:5]))
     lines += ['', 'Top warp-stall reasons (share of stalled issue slots):', ''] + stalls_out
+    if a.hot > 0:
+        lines += hot_instructions(a.report, a.kernel, a.hot)
     text = '\n'.join(lines) + '\n'
     if a.out:
         with open(a.out, 'w') as f:
