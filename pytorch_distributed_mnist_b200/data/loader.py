@@ -64,10 +64,13 @@ class ShardSampler(object):
     def set_epoch(self, epoch):
         self.epoch = epoch
 
-    def indices(self):
+    def indices(self, epoch=None):
+        """This rank's sample order for ``epoch`` (default: the epoch set by ``set_epoch``).  Pure:
+        safe to call for several epochs from several threads."""
+        epoch = self.epoch if epoch is None else epoch
         if self.shuffle:
             g = torch.Generator()
-            g.manual_seed(self.seed + self.epoch)
+            g.manual_seed(self.seed + epoch)
             idx = torch.randperm(self.length, generator=g)
         else:
             idx = torch.arange(self.length)
@@ -132,13 +135,7 @@ class MNISTDataLoader(object):
     # -- index plan ---------------------------------------------------------
     def _one_epoch(self, epoch_offset=0):
         if self.sampler is not None:
-            if epoch_offset:
-                base = self.sampler.epoch
-                self.sampler.set_epoch(base + epoch_offset)
-                idx = self.sampler.indices()
-                self.sampler.set_epoch(base)
-                return idx
-            return self.sampler.indices()
+            return self.sampler.indices(self.sampler.epoch + epoch_offset)
         if self.shuffle:
             return torch.randperm(len(self.labels))
         return torch.arange(len(self.labels))
@@ -147,12 +144,11 @@ class MNISTDataLoader(object):
         """The sample order for one pass, as an int64 tensor."""
         if self.samples_per_epoch is None:
             return self._one_epoch()
-        want, parts, have, k = int(self.samples_per_epoch), [], 0, 0
-        while have < want:
-            part = self._one_epoch(k)
-            parts.append(part)
-            have += part.numel()
-            k += 1
+        want = int(self.samples_per_epoch)
+        per_part = self.sampler.num_samples if self.sampler is not None else len(self.labels)
+        n_parts = max(1, -(-want // max(1, per_part)))
+        # (building the permutations on a thread pool was tried: slower, torch.randperm is already the whole cost)
+        parts = [self._one_epoch(k) for k in range(n_parts)]
         return torch.cat(parts)[:want].contiguous()
 
     # -- iteration ----------------------------------------------------------
