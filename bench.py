@@ -18,6 +18,11 @@ Two numbers per run, both whole-job aggregates (max over ranks of the time):
   over an ``MNISTDataLoader``): every step includes the host->device copy of that step's
   inputs from pinned host memory and a device->host read of the step's {loss, correct}.
 
+With ``--gpus 1`` the JSON line also carries ``cnn_extension``: the single-GPU training step of the
+CNN that BASELINE.json's configs 2-4 name (not in the reference), ours vs cuDNN/cuBLAS TF32 + Adam,
+measured by ``benchmarks/bench_cnn.py`` in a separate process after the headline numbers are final
+(``--no-cnn`` skips it).
+
 The reference arm builds the reference's own ``Net`` / ``MNISTDataLoader`` / ``Trainer``
 exactly as its ``run()`` does (ref:185-223: stock DDP, ``torch.optim.Adam``) and times its
 ``Trainer.train()``; nothing from this package is on its timed path (this package only
@@ -238,12 +243,71 @@ def run_ours(opts):
         'gpu_launches': launches,
         'impl': 'ours',
     }
+    if world == 1 and opts.cnn:
+        sync_all(dist, device)
+        out['cnn_extension'] = cnn_extension_numbers()
     if rank == 0:
         print(json.dumps(out), flush=True)
     trainer.close()
     sync_all(dist, device)
     model.close()
     dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------ CNN extension (supplementary)
+def run_json_lines(cmd, timeout_s, env=None):
+    """Run ``cmd`` in its own process and return the JSON objects it printed, one per line.  Never
+    raises: a failure comes back as ``[{'unavailable': reason}]`` (the headline number must not depend on it)."""
+    import subprocess
+    try:
+        proc = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout_s, env=env, cwd=ROOT)
+    except subprocess.TimeoutExpired:
+        return [{'unavailable': 'timed out after {} s'.format(timeout_s)}]
+    except OSError as e:
+        return [{'unavailable': '{}: {}'.format(type(e).__name__, e)}]
+    rows = []
+    for line in proc.stdout.splitlines():
+        line = line.strip()
+        if line.startswith('{') and line.endswith('}'):
+            try:
+                rows.append(json.loads(line))
+            except ValueError:
+                pass
+    if proc.returncode != 0 or not rows:
+        tail = (proc.stderr or proc.stdout or '').strip().splitlines()[-1:] or ['no output']
+        rows.append({'unavailable': 'exit code {}: {}'.format(proc.returncode, tail[0][:200])})
+    return rows
+
+
+def cnn_extension_numbers():
+    """BASELINE.json's configs 2-4 also name an MNIST CNN (an extension: the reference has none).
+    Its single-GPU training step through our native step executor vs the same module on cuDNN/cuBLAS TF32 +
+    torch.optim.Adam, measured by benchmarks/bench_cnn.py in a separate process after the headline numbers
+    are final, so that nothing here can disturb or block them."""
+    import socket
+    env = {k: v for k, v in os.environ.items()
+           if k not in ('RANK', 'LOCAL_RANK', 'WORLD_SIZE', 'MASTER_ADDR', 'MASTER_PORT', 'GROUP_RANK', 'LOCAL_WORLD_SIZE')}
+    out = {}
+    for width, batch in ((1, 512), (8, 128)):
+        sock = socket.socket()
+        sock.bind(('127.0.0.1', 0))
+        env['MASTER_PORT'] = str(sock.getsockname()[1])
+        sock.close()
+        rows = run_json_lines([sys.executable, os.path.join(ROOT, 'benchmarks', 'bench_cnn.py'), '--width', str(width),
+                               '--batch', str(batch), '--steps', '40', '--warmup', '10', '--impl', 'engine,stock'],
+                              timeout_s=120, env=env)
+        entry = {'per_gpu_batch': batch}
+        for r in rows:
+            if 'unavailable' in r:
+                entry['unavailable'] = r['unavailable']
+            elif r.get('impl') == 'engine':
+                entry.update({'ms_per_step': r['ms_per_step'], 'images_per_s': r['images_per_s'], 'params': r['params']})
+            elif r.get('impl') == 'stock':
+                entry.update({'stock_ms_per_step': r['ms_per_step'], 'stock_images_per_s': r['images_per_s']})
+        out['width{}'.format(width)] = entry
+    out['note'] = ('supplementary, 1 GPU, device-timed: models.CNN (PyTorch-examples MNIST net x width) training step on the '
+                   'tcgen05/TMA kernels + native step executor vs the same module on cuDNN/cuBLAS TF32 + torch.optim.Adam')
+    return out
 
 
 # ------------------------------------------------------------------------------ reference arm
@@ -365,6 +429,8 @@ def main():
     ap.add_argument('--comm', choices=('auto', 'peer', 'group'), default='auto')
     ap.add_argument('--placement', choices=('auto', 'staged', 'zerocopy'), default='auto',
                     help='e2e input path (ours); both move every step\'s inputs from pinned host memory')
+    ap.add_argument('--no-cnn', dest='cnn', action='store_false',
+                    help='skip the supplementary single-GPU CNN-extension numbers (ours, --gpus 1 only)')
     opts = ap.parse_args()
     if opts.steps < 1:
         raise SystemExit('--steps must be >= 1')
