@@ -285,8 +285,12 @@ def cnn_extension_numbers():
     torch.optim.Adam, measured by benchmarks/bench_cnn.py in a separate process after the headline numbers
     are final, so that nothing here can disturb or block them."""
     import socket
+    # a clean single-rank environment: under torchrun the parent's rendezvous variables (in particular
+    # TORCHELASTIC_USE_AGENT_STORE, which turns env:// into a client of the agent's store) must not leak
     env = {k: v for k, v in os.environ.items()
-           if k not in ('RANK', 'LOCAL_RANK', 'WORLD_SIZE', 'MASTER_ADDR', 'MASTER_PORT', 'GROUP_RANK', 'LOCAL_WORLD_SIZE')}
+           if k not in ('RANK', 'LOCAL_RANK', 'WORLD_SIZE', 'MASTER_ADDR', 'MASTER_PORT', 'GROUP_RANK', 'LOCAL_WORLD_SIZE',
+                        'ROLE_RANK', 'ROLE_WORLD_SIZE', 'GROUP_WORLD_SIZE', 'ROLE_NAME')
+           and not k.startswith('TORCHELASTIC_')}
     out = {}
     for width, batch in ((1, 512), (8, 128)):
         sock = socket.socket()
