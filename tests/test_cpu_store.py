@@ -60,3 +60,35 @@ def test_store_get_times_out():
         st.get('never-published')
     assert 0.5 < time.time() - t0 < 10
     st.close()
+
+
+def test_store_concurrent_clients():
+    """Eight clients hammering one server (set / add / blocking get of a neighbour's key): the
+    counter must be exact and every value intact."""
+    import threading
+    from pytorch_distributed_mnist_b200.parallel.store import NativeStore
+    port = _port()
+    server = NativeStore('127.0.0.1', port, is_server=True, timeout_s=30)
+    errs, clients, rounds = [], 8, 120
+
+    def client(i):
+        try:
+            st = NativeStore('127.0.0.1', port, is_server=False, timeout_s=30)
+            for k in range(rounds):
+                st.set('k/{}/{}'.format(i, k), bytes([i]) * (k % 97 + 1))
+                st.add('ctr', 1)
+                if k % 10 == 0:
+                    j = (i + 1) % clients
+                    assert st.get('k/{}/{}'.format(j, k)) == bytes([j]) * (k % 97 + 1)
+            st.close()
+        except Exception as e:  # noqa: BLE001
+            errs.append(repr(e))
+
+    threads = [threading.Thread(target=client, args=(i,)) for i in range(clients)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(90)
+    assert not errs and not any(t.is_alive() for t in threads), errs[:3]
+    assert server.add('ctr', 0) == clients * rounds
+    server.close()
