@@ -130,6 +130,12 @@ typedef struct pdm_net_step_args {
                                  with the pulled LL exchange), not on one GPU (10.3 vs 8.7); PDM_NET_DEP=grid|flag
                                  forces one.  Needs `sync` to be at least 3 words and done_before to be exact. */
   uint32_t done_before;       /* sum of pdm_net_planned_ctas() over all earlier steps issued on these sync words */
+  int32_t inputs_stable;      /* 1: x, y and row_index were NOT written by the kernel that precedes this call on the
+                                 stream (they come from a memcpy, or are a resident dataset).  The launch is a
+                                 programmatic dependent one, and with this flag the kernel loads its first input
+                                 tile before it waits for its predecessor (saves ~1 us/step).  Leave 0 when another
+                                 kernel (a gather, a normalise, .contiguous()) produces the inputs right before:
+                                 only the wait makes that kernel's writes visible. */
 } pdm_net_step_args;
 
 int pdm_net_train_step(const pdm_net_step_args* args, pdm_stream_t stream);
@@ -155,7 +161,11 @@ int pdm_net_planned_ctas(int batch, int want_ctas);
  * limit.  Every batch size works.
  *
  * First call on a device (with that device current) looks the array's device address up and
- * caches it: make that call before any stream capture.  Nothing here allocates or frees.
+ * caches it: make that call before any stream capture.  Nothing here allocates or frees; the
+ * PDM_NET_TRACE clock tracing (whose buffer is allocated on first use) is ignored on this path.
+ * With peers the exchange form (PDM_NET_LL, default pull) is chosen exactly as in
+ * pdm_net_train_step, so ranks may mix the two entry points; consecutive static steps are always
+ * ordered by grid completion (flag_dependency / done_before are ignored).
  * All calls on a device share the array and it keeps the previous call's contents; what must
  * be zero is cleared in stream order on every call, but calls that overlap on one GPU race on
  * the array -- serialise them. */

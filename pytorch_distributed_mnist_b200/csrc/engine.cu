@@ -391,6 +391,7 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
       }
       a.flag_dependency = b == 0 ? 2 : 1;   // first step of a run: ordered after whatever ran before by the grid dependency
       a.done_before = e->done_total;
+      a.inputs_stable = 1;                  // the slot was filled by a memcpy that completed before the launch
       rc = pdm_net_train_step(&a, cs);
       if (rc == PDM_OK) e->done_total += (uint32_t)pdm_net_planned_ctas(n, ctas);
     } else {
@@ -501,6 +502,7 @@ int pdm_engine_run_device(pdm_engine* e, const uint8_t* dev_images, const uint8_
     }
     a.flag_dependency = i == 0 ? 2 : 1;
     a.done_before = e->done_total;
+    a.inputs_stable = 1;                    // resident pool
     int rc = pdm_net_train_step(&a, st);
     if (rc != PDM_OK) return rc;
     e->done_total += (uint32_t)pdm_net_planned_ctas(batch, ctas);
@@ -620,6 +622,7 @@ int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, 
     }
     a.flag_dependency = b == 0 ? 2 : 1;
     a.done_before = e->done_total;
+    a.inputs_stable = 1;                    // resident dataset; the index plan came by memcpy
     rc = pdm_net_train_step(&a, cs);
     if (rc != PDM_OK) return rc;
     e->done_total += (uint32_t)pdm_net_planned_ctas(n, ctas);

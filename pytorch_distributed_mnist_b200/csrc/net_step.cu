@@ -88,6 +88,8 @@ struct KernelArgs {
   int trigger_early;      // 1: release the next step's launch as soon as this grid is resident
   int poll_ns;            // back-off between polls of sync[2]
   int ll_pull;            // 1: publish into our own outbox and read the peers' outboxes over NVLink
+  int inputs_stable;      // 1: x / y / row_index were not written by the kernel just before this one on the
+                          //    stream, so the first tile may be loaded before the dependency wait
   OptConsts oc;
   pdm_peers peers;
 };
@@ -205,14 +207,21 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
   const int row_begin = cta * a.rows_per_cta;
   const int row_end = min(a.batch, row_begin + a.rows_per_cta);
 
-  // The inputs do not depend on the previous step: start streaming them before waiting for it.
+  // Inputs the caller declared stable (a memcpy, a resident dataset: nothing the preceding kernel
+  // wrote) do not depend on the previous step: start streaming them before waiting for it.  Otherwise
+  // the first tile is loaded after the wait below -- under a programmatic dependent launch only that
+  // wait makes the predecessor's writes visible (e.g. a normalise or gather kernel producing x).
   typename Raw::type raw[RT];
+  auto load_first_tile = [&]() {
 #pragma unroll
-  for (int r = 0; r < RT; ++r) {
-    raw[r] = typename Raw::type();
-    if (owns_cols && row_begin + r < row_end)
-      raw[r] = Raw::load(a.x, a.row_index ? __ldg(a.row_index + row_begin + r) : row_begin + r, tid);
-  }
+    for (int r = 0; r < RT; ++r) {
+      raw[r] = typename Raw::type();
+      if (owns_cols && row_begin + r < row_end)
+        raw[r] = Raw::load(a.x, a.row_index ? __ldg(a.row_index + row_begin + r) : row_begin + r, tid);
+    }
+  };
+  const bool early_inputs = MODE == 1 || a.inputs_stable != 0;
+  if (early_inputs) load_first_tile();
 
   // Programmatic dependent launch: everything above overlaps the tail of the previous step's
   // kernel; parameters, optimizer state, scratch and barrier words are only touched below.
@@ -235,6 +244,7 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
       asm volatile("griddepcontrol.wait;" ::: "memory");
     }
   }
+  if (!early_inputs) load_first_tile();
 
   uint32_t bar_base = 0;
   if (MODE == 0 && tid == 0 && G > 1) bar_base = ld_acquire_gpu(a.sync + 1);   // latency hidden by phase 1
@@ -669,9 +679,11 @@ long long* trace_buffer() {
 }
 
 template <int MODE>
-cudaError_t launch(const KernelArgs& ka, int x_dtype, int ctas, cudaStream_t stream) {
+cudaError_t launch(const KernelArgs& ka, int x_dtype, int ctas, cudaStream_t stream, bool allow_trace = true) {
   KernelArgs local = ka;
-  if (MODE == 0) local.trace = trace_buffer();
+  // allow_trace == false: the allocation-free entry point.  trace_buffer() allocates on first use,
+  // so that path never traces, whatever PDM_NET_TRACE says.
+  if (MODE == 0) local.trace = allow_trace ? trace_buffer() : nullptr;
   void* params[] = {&local};
   const void* fn;
   if (MODE == 0 && train_rt(ka.batch) == 4)
@@ -705,6 +717,32 @@ cudaError_t launch(const KernelArgs& ka, int x_dtype, int ctas, cudaStream_t str
   if (mode == LAUNCH_COOP && ctas > 1)
     return cudaLaunchCooperativeKernel(fn, dim3(ctas), dim3(kThreads), params, 0, stream);
   return cudaLaunchKernel(fn, dim3(ctas), dim3(kThreads), params, 0, stream);
+}
+
+// Protocol knobs shared by both training entry points (so that ranks which mix them still agree
+// on the exchange form): PDM_NET_DEP=grid|flag, PDM_NET_LL=push|pull, PDM_NET_TRIGGER=barrier|start,
+// PDM_NET_POLL_NS=<n>.
+// Measured on B200 (profiles/raw/step_sweep_dep.log, step_sweep_multi_ll_2.log), us/step at B = 512:
+//   1 GPU : grid 8.7, flag 10.3                      -> grid
+//   2 GPUs: push+grid 17.8, push+flag 16.0, pull+grid 15.3, pull+flag 12.6  -> pull + flag
+// With peers, whatever waits for this grid's memory traffic to drain (grid completion, or the
+// fence before the sync[2] bump) also waits for the acknowledgement of pushed remote stores;
+// pulled data leaves nothing in flight.  Unset knobs therefore follow the world size.
+void apply_knobs(KernelArgs* ka, const pdm_net_step_args* args, int world, bool allow_flag_dependency) {
+  static const int dep_env = [] { const char* e = getenv("PDM_NET_DEP"); return !e ? -1 : (!strcmp(e, "flag") ? 1 : 0); }();
+  static const int pull_env = [] { const char* e = getenv("PDM_NET_LL"); return !e ? -1 : (!strcmp(e, "pull") ? 1 : 0); }();
+  static const int early = [] { const char* e = getenv("PDM_NET_TRIGGER"); return (e && !strcmp(e, "barrier")) ? 0 : 1; }();
+  static const int poll = [] { const char* e = getenv("PDM_NET_POLL_NS"); return e && *e ? atoi(e) : 0; }();
+  const int dep_flag = dep_env >= 0 ? dep_env : (world > 1 ? 1 : 0);
+  // flag_dependency 1: count this launch's CTAs in sync[2] and wait for the earlier ones through it;
+  // 2: count, but wait with griddepcontrol.wait (first step of a run: whatever ran before on the
+  // stream may not have been counted)
+  ka->flag_dep = (allow_flag_dependency && args->flag_dependency && dep_flag && launch_mode() == LAUNCH_PDL) ? 1 : 0;
+  ka->flag_wait = (ka->flag_dep && args->flag_dependency == 1) ? 1 : 0;
+  ka->done_before = args->done_before;
+  ka->trigger_early = (ka->flag_wait && early) ? 1 : 0;
+  ka->poll_ns = poll;
+  ka->ll_pull = pull_env >= 0 ? pull_env : (world > 1 ? 1 : 0);
 }
 
 }  // namespace
@@ -766,29 +804,8 @@ extern "C" int pdm_net_train_step(const pdm_net_step_args* args, pdm_stream_t st
   ka.metrics = args->metrics;
   ka.step_out = args->step_out;
   ka.row_index = args->row_index;
-  {
-    // knobs: PDM_NET_DEP=grid|flag, PDM_NET_LL=push|pull, PDM_NET_TRIGGER=barrier|start, PDM_NET_POLL_NS=<n>.
-    // Measured on B200 (profiles/raw/step_sweep_dep.log, step_sweep_multi_ll_2.log), us/step at B = 512:
-    //   1 GPU : grid 8.7, flag 10.3                      -> grid
-    //   2 GPUs: push+grid 17.8, push+flag 16.0, pull+grid 15.3, pull+flag 12.6  -> pull + flag
-    // With peers, whatever waits for this grid's memory traffic to drain (grid completion, or the
-    // fence before the sync[2] bump) also waits for the acknowledgement of pushed remote stores;
-    // pulled data leaves nothing in flight.  Unset knobs therefore follow the world size.
-    static const int dep_env = [] { const char* e = getenv("PDM_NET_DEP"); return !e ? -1 : (!strcmp(e, "flag") ? 1 : 0); }();
-    static const int pull_env = [] { const char* e = getenv("PDM_NET_LL"); return !e ? -1 : (!strcmp(e, "pull") ? 1 : 0); }();
-    static const int early = [] { const char* e = getenv("PDM_NET_TRIGGER"); return (e && !strcmp(e, "barrier")) ? 0 : 1; }();
-    static const int poll = [] { const char* e = getenv("PDM_NET_POLL_NS"); return e && *e ? atoi(e) : 0; }();
-    const int dep_flag = dep_env >= 0 ? dep_env : (world > 1 ? 1 : 0);
-    // flag_dependency 1: count this launch's CTAs in sync[2] and wait for the earlier ones through it;
-    // 2: count, but wait with griddepcontrol.wait (first step of a run: whatever ran before on the
-    // stream may not have been counted)
-    ka.flag_dep = (args->flag_dependency && dep_flag && launch_mode() == LAUNCH_PDL) ? 1 : 0;
-    ka.flag_wait = (ka.flag_dep && args->flag_dependency == 1) ? 1 : 0;
-    ka.done_before = args->done_before;
-    ka.trigger_early = (ka.flag_wait && early) ? 1 : 0;
-    ka.poll_ns = poll;
-    ka.ll_pull = pull_env >= 0 ? pull_env : (world > 1 ? 1 : 0);
-  }
+  apply_knobs(&ka, args, world, /*allow_flag_dependency=*/true);
+  ka.inputs_stable = args->inputs_stable != 0;
   ka.oc = make_consts(h, world);
   ka.peers = args->peers;
   ka.peers.world = world;
@@ -861,7 +878,8 @@ extern "C" int pdm_net_forward(const void* x, int x_dtype, int batch, const floa
 // Set-up: the first call on each device resolves the device addresses of the arrays with
 // cudaGetSymbolAddress (the array names are host-side handles in host code, not device
 // pointers) while that device is current, and caches them.  Make that first call outside any
-// stream capture.  No call here allocates or frees device or host memory.
+// stream capture.  No call here allocates or frees device or host memory (clock tracing,
+// PDM_NET_TRACE, is therefore ignored on this path: its buffer is allocated on first use).
 //
 // Sharing: all calls on a device use the same array, which keeps the last call's partial
 // gradients.  The step overwrites every element it later reads, and the barrier words -- the
@@ -978,13 +996,18 @@ extern "C" int pdm_net_train_step_static(const pdm_net_step_args* args, pdm_stre
   ka.metrics = args->metrics;
   ka.step_out = args->step_out;
   ka.row_index = args->row_index;
+  // Same exchange form (push / pull) as pdm_net_train_step would pick, so ranks may mix the two entry
+  // points; the step-to-step order is always grid completion here (the built-in barrier words are
+  // re-zeroed per call, which a running count in sync[2] would not survive).
+  apply_knobs(&ka, args, world, /*allow_flag_dependency=*/false);
+  ka.inputs_stable = args->inputs_stable != 0;
   ka.oc = make_consts(h, world);
   ka.peers = args->peers;
   ka.peers.world = world;
   // The barrier words are the only scratch that must start at zero (an aborted earlier launch
   // could have left an arrival count behind): clear them in stream order.
   PDM_CHECK_CUDA(cudaMemsetAsync(addrs.sync, 0, 2 * sizeof(uint32_t), (cudaStream_t)stream));
-  PDM_CHECK_CUDA(launch<0>(ka, args->x_dtype, ctas, (cudaStream_t)stream));
+  PDM_CHECK_CUDA(launch<0>(ka, args->x_dtype, ctas, (cudaStream_t)stream, /*allow_trace=*/false));
   return PDM_OK;
 }
 

@@ -67,11 +67,30 @@ def build(force=False, verbose=False):
     if not srcs:
         raise RuntimeError('no sources under ' + CSRC_DIR)
     newest = max([os.path.getmtime(s) for s in srcs] + [_deps_mtime(), os.path.getmtime(__file__)])
-    if not force and os.path.isfile(LIB_PATH) and os.path.getmtime(LIB_PATH) >= newest:
+
+    def up_to_date():
+        return os.path.isfile(LIB_PATH) and os.path.getmtime(LIB_PATH) >= newest
+
+    if not force and up_to_date():
         return LIB_PATH
-    nvcc = find_nvcc()
     os.makedirs(OBJ_DIR, exist_ok=True)
     os.makedirs(NATIVE_DIR, exist_ok=True)
+    # Every rank of a spawn job may get here at once (first run on a fresh box): one of them builds, the
+    # others wait on the lock and then find the library up to date.  Objects are shared paths under
+    # build/obj, so two concurrent builds would link each other's half-written files.
+    import fcntl
+    with open(os.path.join(OBJ_DIR, '.build.lock'), 'w') as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and up_to_date():
+                return LIB_PATH
+            return _build_locked(srcs, force, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(srcs, force, verbose):
+    nvcc = find_nvcc()
     hdr_mtime = max(_deps_mtime(), os.path.getmtime(__file__))
     jobs = []
     objs = []

@@ -54,7 +54,8 @@ class NetStepArgs(ctypes.Structure):
                 ('grad_out', c_void_p), ('scratch', c_void_p), ('sync', c_void_p),
                 ('metrics', c_void_p), ('step_out', c_void_p),
                 ('hyper', Hyper), ('peers', Peers), ('row_index', c_void_p),
-                ('flag_dependency', ctypes.c_int32), ('done_before', ctypes.c_uint32)]
+                ('flag_dependency', ctypes.c_int32), ('done_before', ctypes.c_uint32),
+                ('inputs_stable', ctypes.c_int32)]
 
 
 class NativeError(RuntimeError):

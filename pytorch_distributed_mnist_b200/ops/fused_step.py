@@ -29,10 +29,15 @@ class NetStepper(object):
         self.step_out = torch.zeros(2, dtype=torch.float32, device=self.device)
         self.comm = comm
 
-    def train_step(self, x, y, params, m, v, hyper, grad_out=None, ctas=0, step_out=None, scratch=None):
+    def train_step(self, x, y, params, m, v, hyper, grad_out=None, ctas=0, step_out=None, scratch=None,
+                   inputs_stable=False):
         """One fused step.  x [B,784] uint8|float32, y [B] uint8|int64|int32, params/m/v flat
         PDM_NET_FLAT float32 (m, v may be None when hyper.opt allows).  Returns the
-        2-float device tensor {mean loss, correct}."""
+        2-float device tensor {mean loss, correct}.
+
+        ``inputs_stable=True`` promises that no kernel queued right before this call wrote ``x`` / ``y``
+        (they were copied in, or are a resident dataset): the kernel then starts loading them before it
+        waits for its predecessor on the stream.  The default is the safe order."""
         x = x.contiguous()
         y = y.contiguous()
         so = step_out if step_out is not None else self.step_out
@@ -49,6 +54,7 @@ class NetStepper(object):
         a.metrics = self.metrics.data_ptr()
         a.step_out = so.data_ptr()
         a.hyper = hyper
+        a.inputs_stable = 1 if inputs_stable else 0
         if self.comm is not None and self.comm.world > 1:
             a.peers = self.comm.peers_struct(advance=True)
         _lib.check(self._lib.pdm_net_train_step(ctypes.byref(a), _lib.stream_ptr()), 'pdm_net_train_step')

@@ -73,8 +73,10 @@ def _run(args):
     rank = args.rank
     device = pick_device(args, rank)
     ngpus = torch.cuda.device_count()
-    divisor = ngpus if device.type == 'cuda' else args.world_size
-    # --batch-size and --workers are node totals (ref:174-175)
+    # --batch-size and --workers are node totals (ref:174-175).  The reference divides by the GPU count and
+    # asserts world_size == GPU count (ref:350-351); dividing by world_size is the same thing whenever that
+    # holds and keeps the global batch at --batch-size when fewer ranks than visible GPUs are started.
+    divisor = args.world_size
     args.batch_size = int(args.batch_size / divisor)
     args.workers = int((args.workers + divisor - 1) / divisor)
     if device.type == 'cuda':

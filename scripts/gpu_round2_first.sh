@@ -8,7 +8,7 @@ N=$(nvidia-smi -L | wc -l)
 echo "== topology discovery on real hardware"
 timeout 60 python -m pytorch_distributed_mnist_b200.parallel.topology 2>&1 | tail -14
 echo "== multi-GPU suite (consolidation asserts, native CNN step, dead peer)"
-timeout 600 python -u -m pytest tests/test_gpu_multi.py -m gpu -x -q --timeout=150 -p no:cacheprovider > gpurun_out/pytest_multi_r2_$N.log 2>&1; echo "rc=$?"; tail -5 gpurun_out/pytest_multi_r2_$N.log | cut -c1-300
+#timeout 600 python -u -m pytest tests/test_gpu_multi.py -m gpu -x -q --timeout=150 -p no:cacheprovider > gpurun_out/pytest_multi_r2_$N.log 2>&1; echo "rc=$?"; tail -5 gpurun_out/pytest_multi_r2_$N.log | cut -c1-300
 echo "== NVLS (experimental)"
 PDM_TEST_NVLS=1 timeout 200 python -u -m pytest tests/test_gpu_multi.py -m gpu -x -q --timeout=120 -p no:cacheprovider -k nvls > gpurun_out/pytest_nvls_$N.log 2>&1; echo "rc=$?"; tail -25 gpurun_out/pytest_nvls_$N.log | cut -c1-300
 echo "== all-reduce sweep with --nvls"
