@@ -17,11 +17,20 @@ Two numbers per run, both whole-job aggregates (max over ranks of the time):
 * ``e2e``    -- the same metric through the public API a user calls (``Trainer.train()``
   over an ``MNISTDataLoader``): every step includes the host->device copy of that step's
   inputs from pinned host memory and a device->host read of the step's {loss, correct}.
+  ``e2e.value`` is images / WALL time of the ``Trainer.train()`` call (host clock around the
+  call, barrier + synchronize on both sides, max over ranks); the CUDA-event span of the same
+  pass is reported beside it as ``device_ms_per_step``.
 
-With ``--gpus 1`` the JSON line also carries ``cnn_extension``: the single-GPU training step of the
-CNN that BASELINE.json's configs 2-4 name (not in the reference), ours vs cuDNN/cuBLAS TF32 + Adam,
-measured by ``benchmarks/bench_cnn.py`` in a separate process after the headline numbers are final
-(``--no-cnn`` skips it).
+The JSON line also carries, measured in separate processes (one per rank, same launch geometry)
+after the headline numbers are final so that they can neither disturb nor block them:
+
+* ``cnn_extension`` -- the training step of the CNN that BASELINE.json's configs 2-4 name (not in
+  the reference): our native step executor vs stock DistributedDataParallel on cuDNN/cuBLAS TF32 +
+  ``torch.optim.Adam``, width 1 at batch 512/GPU and width 8 at batch 128/GPU, at N GPUs
+  (``benchmarks/bench_cnn.py``; ``--no-cnn`` skips it);
+* ``allreduce_us`` (N > 1) -- the other half of BASELINE.json's metric: the gradient all-reduce
+  per step for the 31,400-byte ``Net`` bucket and for 64 MB, ours (fused with 1/W and Adam) vs
+  NCCL (+ Adam) (``benchmarks/allreduce_sweep.py``; ``--no-allreduce`` skips it).
 
 The reference arm builds the reference's own ``Net`` / ``MNISTDataLoader`` / ``Trainer``
 exactly as its ``run()`` does (ref:185-223: stock DDP, ``torch.optim.Adam``) and times its
@@ -196,23 +205,36 @@ def run_ours(opts):
         ms = max_over_ranks(dist, ms, device)
         wall_ms = max_over_ranks(dist, wall_ms, device)
 
+        # ---- the same K steps on fp32 inputs (what the reference arm reads: 3,136 B/sample + int64 labels) ----
+        del pool_x, pool_y
+        nb32 = REF_POOL_BATCHES
+        pool_xf = torch.randn(nb32 * B, 784, device=device, generator=g)
+        pool_yl = torch.randint(0, 10, (nb32 * B,), device=device, generator=g)
+        sync_all(dist, device)
+        engine.train_device(pool_xf, pool_yl, B, max(W, 3), ctas=opts.ctas)
+        sync_all(dist, device)
+        ms_f32 = max_over_ranks(dist, engine.train_device(pool_xf, pool_yl, B, K, ctas=opts.ctas), device)
+        del pool_xf, pool_yl
+
         # ---- e2e: Trainer.train() over a host dataset ----
         trainer.train_loader = warm_loader
         warm_loader.set_sample_epoch(0)
         trainer.train()
-        trainer.train_loader = timed_loader
-        timed_loader.set_sample_epoch(0)
+        trainer.train_loader = timed_loader          # binds (page-locks / hands over) the dataset: set-up, not a step
+        timed_loader.set_sample_epoch(0)             # ref:231 -- the caller's per-epoch call, before train()
         sync_all(dist, device)
         t0 = time.perf_counter()
         loss_avg, acc = trainer.train()
+        torch.cuda.synchronize(device)               # train() has already read every step's result back
+        e2e_wall_ms = (time.perf_counter() - t0) * 1e3
         sync_all(dist, device)
-        e2e_wall_ms = max_over_ranks(dist, (time.perf_counter() - t0) * 1e3, device)
+        e2e_wall_ms = max_over_ranks(dist, e2e_wall_ms, device)
         e2e_dev_ms = max_over_ranks(dist, trainer.last_train_ms, device)
     clk = clocks.summary()
 
     images = K * B * world
     value = images / (ms / 1e3)
-    e2e_value = images / (e2e_dev_ms / 1e3)
+    e2e_value = images / (e2e_wall_ms / 1e3)
     out = {
         'metric': METRIC, 'value': value, 'unit': 'images/s', 'n_gpus': world, 'steps': K, 'warmup': max(W, 3),
         'ms_per_step': ms / K, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
@@ -223,13 +245,19 @@ def run_ours(opts):
                    'comm': 'peer-memory LL all-reduce fused in the step kernel' if getattr(model, 'uses_peer', False) and world > 1
                            else ('single GPU' if world == 1 else 'torch.distributed fallback'),
                    'l2_policy': 'inputs larger than L2: {} distinct batches = {:.0f} MB cycled'.format(
-                       POOL_BATCHES, POOL_BATCHES * B * 785 / 1e6)},
+                       POOL_BATCHES, POOL_BATCHES * B * 785 / 1e6),
+                   'inputs': 'raw uint8 pixels, normalised in-kernel (bit-exact ToTensor+Normalize); fp32 math'},
         'wall_ms_per_step': wall_ms / K,
+        'fp32_inputs': {'value': images / (ms_f32 / 1e3), 'ms_per_step': ms_f32 / K,
+                        'note': 'same kernel instantiated for already-normalised fp32 pixels + int64 labels, the bytes '
+                                'the reference arm reads (3,144 B/sample); {} distinct batches = {:.0f} MB cycled'.format(
+                                    nb32, nb32 * B * 3144 / 1e6)},
         'clocks': clk,
         'e2e': {'value': e2e_value, 'unit': 'images/s',
                 'h2d_bytes_per_step': B * 785 + (B * 4 if trainer.data_placement == 'zerocopy' else 0),
                 'd2h_bytes_per_step': 8,
-                'ms_per_step': e2e_dev_ms / K, 'wall_ms_per_step': e2e_wall_ms / K, 'steps': K,
+                'ms_per_step': e2e_wall_ms / K, 'timing': 'host wall clock around Trainer.train(), max over ranks',
+                'device_ms_per_step': e2e_dev_ms / K, 'steps': K,
                 'api': 'Trainer.train() over MNISTDataLoader',
                 'input_path': {
                     'staged': 'loader threads gather each shuffled batch into a pinned slot; one cudaMemcpyAsync H2D '
@@ -243,14 +271,18 @@ def run_ours(opts):
         'gpu_launches': launches,
         'impl': 'ours',
     }
-    if world == 1 and opts.cnn:
-        sync_all(dist, device)
-        out['cnn_extension'] = cnn_extension_numbers()
-    if rank == 0:
-        print(json.dumps(out), flush=True)
+    # everything below runs in child processes (one per rank) once the headline numbers are final
     trainer.close()
     sync_all(dist, device)
     model.close()
+    sync_all(dist, device)
+    if opts.cnn:
+        out['cnn_extension'] = cnn_extension_numbers(rank, local, world)
+    if world > 1 and opts.allreduce:
+        out['allreduce_us'] = allreduce_numbers(rank, local, world)
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    sync_all(dist, device)
     dist.destroy_process_group()
 
 
@@ -279,28 +311,35 @@ def run_json_lines(cmd, timeout_s, env=None):
     return rows
 
 
-def cnn_extension_numbers():
-    """BASELINE.json's configs 2-4 also name an MNIST CNN (an extension: the reference has none, SURVEY D1).
-    Its single-GPU training step through our native step executor vs the same module on cuDNN/cuBLAS TF32 +
-    torch.optim.Adam, measured by benchmarks/bench_cnn.py in a separate process after the headline numbers
-    are final, so that nothing here can disturb or block them."""
-    import socket
-    # a clean single-rank environment: under torchrun the parent's rendezvous variables (in particular
-    # TORCHELASTIC_USE_AGENT_STORE, which turns env:// into a client of the agent's store) must not leak
+def child_env(rank, local, world, port):
+    """Environment of this rank's child process: the same rank geometry, a rendezvous of its own.  Under
+    torchrun the parent's TORCHELASTIC_* variables (in particular TORCHELASTIC_USE_AGENT_STORE, which turns
+    env:// into a client of the agent's store) must not leak."""
     env = {k: v for k, v in os.environ.items()
-           if k not in ('RANK', 'LOCAL_RANK', 'WORLD_SIZE', 'MASTER_ADDR', 'MASTER_PORT', 'GROUP_RANK', 'LOCAL_WORLD_SIZE',
-                        'ROLE_RANK', 'ROLE_WORLD_SIZE', 'GROUP_WORLD_SIZE', 'ROLE_NAME')
+           if k not in ('GROUP_RANK', 'LOCAL_WORLD_SIZE', 'ROLE_RANK', 'ROLE_WORLD_SIZE', 'GROUP_WORLD_SIZE', 'ROLE_NAME')
            and not k.startswith('TORCHELASTIC_')}
+    env.update({'RANK': str(rank), 'LOCAL_RANK': str(local), 'WORLD_SIZE': str(world), 'MASTER_ADDR': '127.0.0.1',
+                'MASTER_PORT': str(port)})
+    return env
+
+
+def child_port(offset):
+    """A rendezvous port every rank derives identically (children of all ranks must meet on it)."""
+    base = int(os.environ.get('MASTER_PORT', '29533'))
+    return 20000 + (base * 7 + 131 * offset) % 20000
+
+
+def cnn_extension_numbers(rank, local, world):
+    """BASELINE.json's configs 2-4 also name an MNIST CNN (an extension: the reference has none, SURVEY D1).
+    Its training step through our native step executor vs the same module under stock DistributedDataParallel on
+    cuDNN/cuBLAS TF32 + torch.optim.Adam, at this run's GPU count: every rank starts benchmarks/bench_cnn.py as a
+    child with its own rank geometry (device-timed there, max over ranks), rank 0 reports."""
     out = {}
-    for width, batch in ((1, 512), (8, 128)):
-        sock = socket.socket()
-        sock.bind(('127.0.0.1', 0))
-        env['MASTER_PORT'] = str(sock.getsockname()[1])
-        sock.close()
+    for k, (width, batch) in enumerate(((1, 512), (8, 128))):
         rows = run_json_lines([sys.executable, os.path.join(ROOT, 'benchmarks', 'bench_cnn.py'), '--width', str(width),
                                '--batch', str(batch), '--steps', '40', '--warmup', '10', '--impl', 'engine,stock'],
-                              timeout_s=120, env=env)
-        entry = {'per_gpu_batch': batch}
+                              timeout_s=180, env=child_env(rank, local, world, child_port(1 + k)))
+        entry = {'per_gpu_batch': batch, 'n_gpus': world}
         for r in rows:
             if 'unavailable' in r:
                 entry['unavailable'] = r['unavailable']
@@ -308,9 +347,29 @@ def cnn_extension_numbers():
                 entry.update({'ms_per_step': r['ms_per_step'], 'images_per_s': r['images_per_s'], 'params': r['params']})
             elif r.get('impl') == 'stock':
                 entry.update({'stock_ms_per_step': r['ms_per_step'], 'stock_images_per_s': r['images_per_s']})
+        if 'ms_per_step' in entry and 'stock_ms_per_step' in entry:
+            entry['speedup_vs_stock'] = entry['stock_ms_per_step'] / entry['ms_per_step']
         out['width{}'.format(width)] = entry
-    out['note'] = ('supplementary, 1 GPU, device-timed: models.CNN (PyTorch-examples MNIST net x width) training step on the '
-                   'tcgen05/TMA kernels + native step executor vs the same module on cuDNN/cuBLAS TF32 + torch.optim.Adam')
+    out['note'] = ('supplementary, device-timed, max over ranks, weak scaling: models.CNN (PyTorch-examples MNIST net x width) '
+                   'training step on the tcgen05/TMA kernels + native step executor + peer-memory fused all-reduce/Adam vs the '
+                   'same module under torch DistributedDataParallel on cuDNN/cuBLAS TF32 + torch.optim.Adam')
+    return out
+
+
+def allreduce_numbers(rank, local, world):
+    """The gradient all-reduce per step (BASELINE.json metric, second half; config 5) for the reference model's one
+    31,400-byte bucket and for 64 MB: NCCL all-reduce, NCCL + 1/W + torch.optim.Adam (what stock DDP + optimizer do per
+    bucket), our peer-memory all-reduce, and ours fused with 1/W + Adam (what our reducer launches).  us per call,
+    CUDA events, max over ranks; measured by benchmarks/allreduce_sweep.py in child processes."""
+    rows = run_json_lines([sys.executable, os.path.join(ROOT, 'benchmarks', 'allreduce_sweep.py'), '--sizes',
+                           '31408,67108864', '--iters', '100', '--nvls'],
+                          timeout_s=180, env=child_env(rank, local, world, child_port(5)))
+    out = {'n_gpus': world}
+    for r in rows:
+        if 'unavailable' in r:
+            out['unavailable'] = r['unavailable']
+        elif 'bytes' in r:
+            out[str(r['bytes'])] = {k: v for k, v in r.items() if k not in ('bytes', 'world')}
     return out
 
 
@@ -434,7 +493,9 @@ def main():
     ap.add_argument('--placement', choices=('auto', 'staged', 'zerocopy'), default='auto',
                     help='e2e input path (ours); both move every step\'s inputs from pinned host memory')
     ap.add_argument('--no-cnn', dest='cnn', action='store_false',
-                    help='skip the supplementary single-GPU CNN-extension numbers (ours, --gpus 1 only)')
+                    help='skip the supplementary CNN-extension numbers (ours)')
+    ap.add_argument('--no-allreduce', dest='allreduce', action='store_false',
+                    help='skip the all-reduce latency numbers (ours, --gpus > 1)')
     opts = ap.parse_args()
     if opts.steps < 1:
         raise SystemExit('--steps must be >= 1')

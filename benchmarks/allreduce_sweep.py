@@ -47,7 +47,8 @@ def main():
     ap.add_argument('--iters', type=int, default=200)
     ap.add_argument('--warmup', type=int, default=20)
     ap.add_argument('--out', default='')
-    ap.add_argument('--nvls', action='store_true', help='also time the experimental NVLS (multimem) kernel')
+    ap.add_argument('--nvls', action='store_true', help='also time the in-switch (NVLS / multimem) kernel')
+    ap.add_argument('--sizes', default='', help='comma-separated byte sizes (default: the 4 KB - 64 MB sweep)')
     a = ap.parse_args()
     rank, local, world = int(os.environ['RANK']), int(os.environ['LOCAL_RANK']), int(os.environ['WORLD_SIZE'])
     dev = torch.device('cuda', local)
@@ -56,6 +57,8 @@ def main():
     from pytorch_distributed_mnist_b200.ops import _lib
     from pytorch_distributed_mnist_b200.parallel.peer import PeerComm
     sizes = [4 << 10, 16 << 10, 31400 // 4 * 4 + 8, 64 << 10, 256 << 10, 1 << 20, 4 << 20, 16 << 20, 64 << 20]
+    if a.sizes:
+        sizes = [int(x) for x in a.sizes.split(',') if x]
     nmax = max(sizes) // 4
     comm = PeerComm(rank, world, dev, data_bytes=nmax * 4 * 5 + 8192)
     g, out, p, m, v = (comm.data_tensor(nmax) for _ in range(5))
@@ -68,7 +71,7 @@ def main():
             ng, nout, np_, nm, nvv = (nv.data_tensor(nmax) for _ in range(5))
             ng.copy_(g)
             # numerics first: in-switch sum vs the rank-ordered P2P sum (fp32, order may differ)
-            k = 1 << 20
+            k = min(1 << 20, nmax)
             comm.allreduce(g[:k], out[:k], average=True)
             nv.allreduce(ng[:k], nout[:k], average=True)
             torch.cuda.synchronize(dev)

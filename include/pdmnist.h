@@ -396,10 +396,15 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
 int pdm_engine_run_device(pdm_engine* e, const uint8_t* dev_images, const uint8_t* dev_labels,
                           int64_t pool_samples, int batch, int64_t nsteps, const pdm_hyper* hyper,
                           int ctas, float* device_ms);
+/* The same with typed inputs: x PDM_U8 or PDM_F32 (already normalised), y PDM_U8 / PDM_I64 / PDM_I32. */
+int pdm_engine_run_device_typed(pdm_engine* e, const void* dev_images, int x_dtype, const void* dev_labels,
+                                int y_dtype, int64_t pool_samples, int batch, int64_t nsteps,
+                                const pdm_hyper* hyper, int ctas, float* device_ms);
 /* In-kernel gather path (B200-first: the dataset fits HBM many times over).  place: mode 0 copies
  * the dataset to device memory once; mode 1 page-locks + maps the caller's host arrays so the step
- * kernel reads its rows straight from host memory over PCIe (zero-copy).  run_gather uploads the
- * index plan (4 B/sample) once, then issues one launch per step. */
+ * kernel reads its rows straight from host memory over PCIe (zero-copy).  The last four placements
+ * are cached (key: host pointers, length, mode); placing one of them again only selects it.
+ * run_gather uploads the index plan (4 B/sample) once, then issues one launch per step. */
 int pdm_engine_place_dataset(pdm_engine* e, const uint8_t* images, const uint8_t* labels, int64_t n, int mode);
 int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, int batch,
                           const pdm_hyper* hyper, int ctas, float* step_results, float* device_ms);

@@ -59,6 +59,7 @@ bool profile_on() {
 }
 struct HostProf {
   double t[6] = {0, 0, 0, 0, 0, 0};   // wait-filled, h2d+events, launch, record+d2h, sync-old, total
+  double first_wait = 0;              // wait-filled of step 0: worker wake-up + the first gather
   std::chrono::steady_clock::time_point last;
   void start() { last = std::chrono::steady_clock::now(); }
   void lap(int i) {
@@ -100,15 +101,26 @@ struct pdm_engine {
   const uint8_t* images = nullptr;
   const uint8_t* labels = nullptr;
   int64_t n_samples = 0;
-  // dataset as the kernels see it on the in-kernel-gather path (pdm_engine_place_dataset)
-  int placed_mode = -1;                   // -1 none, 0 device copy (owned), 1 host arrays registered + mapped
-  uint8_t* placed_images = nullptr;       // device pointer (copy or alias)
-  uint8_t* placed_labels = nullptr;
-  void* registered_images = nullptr;      // host ranges to unregister
-  void* registered_labels = nullptr;
-  int64_t placed_n = 0;
+  // datasets as the kernels see them on the in-kernel-gather path (pdm_engine_place_dataset): a small
+  // cache, so that switching between loaders (train set / another train set) re-uses the page-locking
+  // or the device copy instead of redoing it inside a training pass
+  struct Placement {
+    int mode = -1;                        // 0 device copy (owned), 1 host arrays registered + mapped
+    const uint8_t* host_images = nullptr; // key
+    const uint8_t* host_labels = nullptr;
+    int64_t n = 0;
+    uint8_t* images = nullptr;            // device pointer (copy or alias)
+    uint8_t* labels = nullptr;
+    uint64_t last_use = 0;
+  };
+  static constexpr int kMaxPlacements = 4;
+  Placement placements[kMaxPlacements];
+  int placed = -1;                        // index of the current placement, -1 = none
+  uint64_t place_clock = 0;
   int32_t* idx_dev = nullptr;             // index plan of the current pass
   int64_t idx_cap = 0;
+  int32_t* idx_host = nullptr;            // pinned staging of the plan (so its upload is truly asynchronous)
+  int64_t idx_host_cap = 0;
   // worker pool
   std::vector<std::thread> workers;
   std::mutex mu;
@@ -302,10 +314,15 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
               e->max_batch);
   PDM_REQUIRE(!train || hyper, PDM_ERR_ARG, "pdm_engine_run: training needs hyper-parameters");
   if (count <= 0) return PDM_OK;
-  for (int64_t i = 0; i < count; ++i)
-    PDM_REQUIRE(indices[i] >= 0 && indices[i] < e->n_samples, PDM_ERR_ARG,
-                "pdm_engine_run: index %lld at position %lld outside [0, %lld)", (long long)indices[i], (long long)i,
-                (long long)e->n_samples);
+  {
+    int64_t lo = indices[0], hi = indices[0];
+    for (int64_t i = 1; i < count; ++i) {
+      lo = indices[i] < lo ? indices[i] : lo;
+      hi = indices[i] > hi ? indices[i] : hi;
+    }
+    PDM_REQUIRE(lo >= 0 && hi < e->n_samples, PDM_ERR_ARG, "pdm_engine_run: index range [%lld, %lld] outside [0, %lld)",
+                (long long)lo, (long long)hi, (long long)e->n_samples);
+  }
   PDM_CHECK_CUDA(cudaSetDevice(e->device));
   const int64_t nsteps = (count + batch - 1) / batch;
   if (train) {
@@ -348,7 +365,7 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
       std::unique_lock<std::mutex> lk(e->mu);
       e->cv_filled.wait(lk, [&] { return e->filled_batch[s] == b; });
     }
-    if (prof) hp.lap(0);
+    if (prof) { hp.lap(0); if (b == 0) hp.first_wait = hp.t[0]; }
     DBG("main issues step %lld (slot %d, n=%d)", (long long)b, s, n);
     // ---- copy stream: device slot s is free once the kernel of step b - slots has run ----
     const size_t bytes = (size_t)n * kSample;
@@ -438,8 +455,9 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
   if (prof) {
     const double tot = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_loop0).count();
     fprintf(stderr, "[pdm_engine] host us/step over %lld steps: wait-staged %.2f | h2d+events %.2f | launch %.2f | "
-            "record %.2f | slot-sync %.2f | loop total %.2f\n", (long long)nsteps, hp.t[0] / nsteps, hp.t[1] / nsteps,
-            hp.t[2] / nsteps, hp.t[3] / nsteps, hp.t[4] / nsteps, tot / nsteps);
+            "record %.2f | slot-sync %.2f | loop total %.2f | first batch ready after %.1f us\n", (long long)nsteps,
+            hp.t[0] / nsteps, hp.t[1] / nsteps, hp.t[2] / nsteps, hp.t[3] / nsteps, hp.t[4] / nsteps, tot / nsteps,
+            hp.first_wait);
   }
   DBG("all steps issued, draining streams");
   cudaStreamSynchronize(e->stream[1]);
@@ -467,13 +485,21 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
   return PDM_OK;
 }
 
-// Run `nsteps` training steps over a DEVICE-resident pool of packed uint8 samples:
-// step i reads batch (i mod (pool_samples / batch)).  No host traffic; one launch per step.
-int pdm_engine_run_device(pdm_engine* e, const uint8_t* dev_images, const uint8_t* dev_labels, int64_t pool_samples,
-                          int batch, int64_t nsteps, const pdm_hyper* hyper, int ctas, float* device_ms) {
+// Run `nsteps` training steps over a DEVICE-resident pool of samples: step i reads batch
+// (i mod (pool_samples / batch)).  No host traffic; one launch per step.  x_dtype PDM_U8 (raw bytes,
+// normalised in-kernel) or PDM_F32 (already normalised, what the reference's loader yields);
+// y_dtype PDM_U8 / PDM_I64 / PDM_I32.
+int pdm_engine_run_device_typed(pdm_engine* e, const void* dev_images, int x_dtype, const void* dev_labels, int y_dtype,
+                                int64_t pool_samples, int batch, int64_t nsteps, const pdm_hyper* hyper, int ctas,
+                                float* device_ms) {
   PDM_REQUIRE(e && dev_images && dev_labels && hyper, PDM_ERR_ARG, "pdm_engine_run_device: NULL argument");
   PDM_REQUIRE(e->params != nullptr, PDM_ERR_STATE, "pdm_engine_run_device: pdm_engine_bind was not called");
   PDM_REQUIRE(batch >= 1 && pool_samples >= batch, PDM_ERR_ARG, "pdm_engine_run_device: pool smaller than one batch");
+  PDM_REQUIRE(x_dtype == PDM_U8 || x_dtype == PDM_F32, PDM_ERR_ARG, "pdm_engine_run_device: x_dtype must be PDM_U8 or PDM_F32");
+  PDM_REQUIRE(y_dtype == PDM_U8 || y_dtype == PDM_I64 || y_dtype == PDM_I32, PDM_ERR_ARG,
+              "pdm_engine_run_device: y_dtype must be PDM_U8, PDM_I64 or PDM_I32");
+  const size_t x_row = (size_t)kImg * (x_dtype == PDM_U8 ? 1 : 4);
+  const size_t y_row = y_dtype == PDM_U8 ? 1 : (y_dtype == PDM_I64 ? 8 : 4);
   PDM_CHECK_CUDA(cudaSetDevice(e->device));
   const int64_t nb = pool_samples / batch;
   cudaStream_t st = e->stream[0];
@@ -482,10 +508,10 @@ int pdm_engine_run_device(pdm_engine* e, const uint8_t* dev_images, const uint8_
     const int64_t b = i % nb;
     pdm_net_step_args a;
     memset(&a, 0, sizeof(a));
-    a.x = dev_images + (size_t)b * batch * kImg;
-    a.x_dtype = PDM_U8;
-    a.y = dev_labels + (size_t)b * batch;
-    a.y_dtype = PDM_U8;
+    a.x = static_cast<const uint8_t*>(dev_images) + (size_t)b * batch * x_row;
+    a.x_dtype = x_dtype;
+    a.y = static_cast<const uint8_t*>(dev_labels) + (size_t)b * batch * y_row;
+    a.y_dtype = y_dtype;
     a.batch = batch;
     a.ctas = ctas;
     a.params = e->params;
@@ -517,51 +543,100 @@ int pdm_engine_run_device(pdm_engine* e, const uint8_t* dev_images, const uint8_
   return PDM_OK;
 }
 
-static void unplace_dataset(pdm_engine* e) {
-  if (e->placed_mode == 0) {
-    if (e->placed_images) cudaFree(e->placed_images);
-    if (e->placed_labels) cudaFree(e->placed_labels);
-  } else if (e->placed_mode == 1) {
-    if (e->registered_images) cudaHostUnregister(e->registered_images);
-    if (e->registered_labels) cudaHostUnregister(e->registered_labels);
+int pdm_engine_run_device(pdm_engine* e, const uint8_t* dev_images, const uint8_t* dev_labels, int64_t pool_samples,
+                          int batch, int64_t nsteps, const pdm_hyper* hyper, int ctas, float* device_ms) {
+  return pdm_engine_run_device_typed(e, dev_images, PDM_U8, dev_labels, PDM_U8, pool_samples, batch, nsteps, hyper, ctas,
+                                     device_ms);
+}
+
+static void drop_placement(pdm_engine::Placement* p) {
+  if (p->mode == 0) {
+    if (p->images) cudaFree(p->images);
+    if (p->labels) cudaFree(p->labels);
+  } else if (p->mode == 1) {
+    if (p->host_images) cudaHostUnregister(const_cast<uint8_t*>(p->host_images));
+    if (p->host_labels) cudaHostUnregister(const_cast<uint8_t*>(p->host_labels));
   }
-  e->placed_mode = -1;
-  e->placed_images = e->placed_labels = nullptr;
-  e->registered_images = e->registered_labels = nullptr;
-  e->placed_n = 0;
+  *p = pdm_engine::Placement();
   cudaGetLastError();
 }
 
-// Make the dataset visible to the in-kernel gather (pdm_engine_run_gather).
+static void unplace_all(pdm_engine* e) {
+  for (auto& p : e->placements) drop_placement(&p);
+  e->placed = -1;
+}
+
+// Make a dataset visible to the in-kernel gather (pdm_engine_run_gather) and select it.
 //   mode 0  copy it into device memory once (60,000 MNIST images are 47 MB of a 180 GB HBM)
 //   mode 1  page-lock and map the caller's host arrays; the step kernel then reads its rows
 //           straight out of host memory over PCIe (zero-copy) -- no staging copy, no H2D memcpy
-// The host arrays must stay alive (mode 1: and unmoved) until the engine is destroyed or re-placed.
+// Up to four placements are kept (keyed by host pointer, length and mode): selecting one that
+// exists costs nothing, so a trainer can switch loaders between passes without paying the
+// page-locking again.  The host arrays must stay alive (mode 1: and unmoved) until the engine is
+// destroyed or the placement is evicted (least recently used first).
 int pdm_engine_place_dataset(pdm_engine* e, const uint8_t* images, const uint8_t* labels, int64_t n, int mode) {
   PDM_REQUIRE(e && images && labels && n >= 1, PDM_ERR_ARG, "pdm_engine_place_dataset: bad arguments");
   PDM_REQUIRE(mode == 0 || mode == 1, PDM_ERR_ARG, "pdm_engine_place_dataset: mode must be 0 (device) or 1 (zero-copy)");
   PDM_REQUIRE(n <= 0x7fffffffLL, PDM_ERR_LIMIT, "pdm_engine_place_dataset: at most 2^31-1 samples");
+  e->place_clock += 1;
+  int victim = 0;
+  for (int i = 0; i < pdm_engine::kMaxPlacements; ++i) {
+    pdm_engine::Placement& p = e->placements[i];
+    if (p.mode == mode && p.host_images == images && p.host_labels == labels && p.n == n) {
+      p.last_use = e->place_clock;
+      e->placed = i;
+      return PDM_OK;
+    }
+    if (p.mode < 0 || (e->placements[victim].mode >= 0 && p.last_use < e->placements[victim].last_use)) victim = i;
+  }
   PDM_CHECK_CUDA(cudaSetDevice(e->device));
-  PDM_CHECK_CUDA(cudaDeviceSynchronize());
-  unplace_dataset(e);
+  pdm_engine::Placement& p = e->placements[victim];
+  if (p.mode >= 0) {
+    PDM_CHECK_CUDA(cudaDeviceSynchronize());    // a queued kernel may still read the evicted placement
+    if (e->placed == victim) e->placed = -1;
+    drop_placement(&p);
+  }
   if (mode == 0) {
-    PDM_CHECK_CUDA(cudaMalloc((void**)&e->placed_images, (size_t)n * kImg));
-    PDM_CHECK_CUDA(cudaMalloc((void**)&e->placed_labels, (size_t)n));
-    e->placed_mode = 0;
-    PDM_CHECK_CUDA(cudaMemcpy(e->placed_images, images, (size_t)n * kImg, cudaMemcpyHostToDevice));
-    PDM_CHECK_CUDA(cudaMemcpy(e->placed_labels, labels, (size_t)n, cudaMemcpyHostToDevice));
+    PDM_CHECK_CUDA(cudaMalloc((void**)&p.images, (size_t)n * kImg));
+    p.mode = 0;
+    PDM_CHECK_CUDA(cudaMalloc((void**)&p.labels, (size_t)n));
+    PDM_CHECK_CUDA(cudaMemcpy(p.images, images, (size_t)n * kImg, cudaMemcpyHostToDevice));
+    PDM_CHECK_CUDA(cudaMemcpy(p.labels, labels, (size_t)n, cudaMemcpyHostToDevice));
+    p.host_images = images;
+    p.host_labels = labels;
   } else {
     cudaError_t ce = cudaHostRegister(const_cast<uint8_t*>(images), (size_t)n * kImg, cudaHostRegisterMapped);
     PDM_REQUIRE(ce == cudaSuccess, PDM_ERR_CUDA, "pdm_engine_place_dataset: cudaHostRegister(images) -> %s", cudaGetErrorString(ce));
-    e->registered_images = const_cast<uint8_t*>(images);
-    e->placed_mode = 1;
+    p.mode = 1;
+    p.host_images = images;
     ce = cudaHostRegister(const_cast<uint8_t*>(labels), (size_t)n, cudaHostRegisterMapped);
-    PDM_REQUIRE(ce == cudaSuccess, PDM_ERR_CUDA, "pdm_engine_place_dataset: cudaHostRegister(labels) -> %s", cudaGetErrorString(ce));
-    e->registered_labels = const_cast<uint8_t*>(labels);
-    PDM_CHECK_CUDA(cudaHostGetDevicePointer((void**)&e->placed_images, e->registered_images, 0));
-    PDM_CHECK_CUDA(cudaHostGetDevicePointer((void**)&e->placed_labels, e->registered_labels, 0));
+    if (ce != cudaSuccess) {
+      drop_placement(&p);
+      pdm_set_error("pdm_engine_place_dataset: cudaHostRegister(labels) -> %s", cudaGetErrorString(ce));
+      return PDM_ERR_CUDA;
+    }
+    p.host_labels = labels;
+    PDM_CHECK_CUDA(cudaHostGetDevicePointer((void**)&p.images, const_cast<uint8_t*>(images), 0));
+    PDM_CHECK_CUDA(cudaHostGetDevicePointer((void**)&p.labels, const_cast<uint8_t*>(labels), 0));
   }
-  e->placed_n = n;
+  p.n = n;
+  p.last_use = e->place_clock;
+  e->placed = victim;
+  // room for the index plan of a whole pass over this set, so that a training pass never allocates
+  if (n > e->idx_cap) {
+    if (e->idx_dev) { PDM_CHECK_CUDA(cudaDeviceSynchronize()); cudaFree(e->idx_dev); }
+    e->idx_dev = nullptr;
+    e->idx_cap = 0;
+    PDM_CHECK_CUDA(cudaMalloc((void**)&e->idx_dev, (size_t)n * sizeof(int32_t)));
+    e->idx_cap = n;
+  }
+  if (e->idx_host_cap < e->idx_cap) {
+    if (e->idx_host) cudaFreeHost(e->idx_host);
+    e->idx_host = nullptr;
+    e->idx_host_cap = 0;
+    PDM_CHECK_CUDA(cudaHostAlloc((void**)&e->idx_host, (size_t)e->idx_cap * sizeof(int32_t), cudaHostAllocDefault));
+    e->idx_host_cap = e->idx_cap;
+  }
   return PDM_OK;
 }
 
@@ -572,37 +647,48 @@ int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, 
                           int ctas, float* step_results, float* device_ms) {
   PDM_REQUIRE(e && indices && hyper, PDM_ERR_ARG, "pdm_engine_run_gather: engine, indices and hyper are required");
   PDM_REQUIRE(e->params != nullptr, PDM_ERR_STATE, "pdm_engine_run_gather: pdm_engine_bind was not called");
-  PDM_REQUIRE(e->placed_mode >= 0, PDM_ERR_STATE, "pdm_engine_run_gather: pdm_engine_place_dataset was not called");
+  PDM_REQUIRE(e->placed >= 0, PDM_ERR_STATE, "pdm_engine_run_gather: pdm_engine_place_dataset was not called");
   PDM_REQUIRE(batch >= 1, PDM_ERR_ARG, "pdm_engine_run_gather: batch must be >= 1");
   if (count <= 0) return PDM_OK;
   PDM_CHECK_CUDA(cudaSetDevice(e->device));
-  std::vector<int32_t> idx32((size_t)count);
-  for (int64_t i = 0; i < count; ++i) {
-    PDM_REQUIRE(indices[i] >= 0 && indices[i] < e->placed_n, PDM_ERR_ARG,
-                "pdm_engine_run_gather: index %lld at position %lld outside [0, %lld)", (long long)indices[i], (long long)i,
-                (long long)e->placed_n);
-    idx32[(size_t)i] = (int32_t)indices[i];
-  }
-  if (count > e->idx_cap) {
+  const pdm_engine::Placement& pl = e->placements[e->placed];
+  if (count > e->idx_cap || count > e->idx_host_cap) {      // a pass longer than the set (several epochs in one plan)
+    PDM_CHECK_CUDA(cudaDeviceSynchronize());
     if (e->idx_dev) cudaFree(e->idx_dev);
-    e->idx_dev = nullptr;
-    e->idx_cap = 0;
+    if (e->idx_host) cudaFreeHost(e->idx_host);
+    e->idx_dev = nullptr; e->idx_host = nullptr;
+    e->idx_cap = e->idx_host_cap = 0;
     PDM_CHECK_CUDA(cudaMalloc((void**)&e->idx_dev, (size_t)count * sizeof(int32_t)));
     e->idx_cap = count;
+    PDM_CHECK_CUDA(cudaHostAlloc((void**)&e->idx_host, (size_t)count * sizeof(int32_t), cudaHostAllocDefault));
+    e->idx_host_cap = count;
+  }
+  {
+    // narrow to 32 bits and range-check in one pass (min/max instead of a branch per element)
+    int64_t lo = indices[0], hi = indices[0];
+    int32_t* dst = e->idx_host;
+    for (int64_t i = 0; i < count; ++i) {
+      const int64_t v = indices[i];
+      lo = v < lo ? v : lo;
+      hi = v > hi ? v : hi;
+      dst[i] = (int32_t)v;
+    }
+    PDM_REQUIRE(lo >= 0 && hi < pl.n, PDM_ERR_ARG, "pdm_engine_run_gather: index range [%lld, %lld] outside [0, %lld)",
+                (long long)lo, (long long)hi, (long long)pl.n);
   }
   const int64_t nsteps = (count + batch - 1) / batch;
   int rc = ensure_results(e, nsteps);
   if (rc != PDM_OK) return rc;
   cudaStream_t cs = e->stream[0];
   PDM_CHECK_CUDA(cudaEventRecord(e->ev_begin, cs));
-  PDM_CHECK_CUDA(cudaMemcpyAsync(e->idx_dev, idx32.data(), (size_t)count * sizeof(int32_t), cudaMemcpyHostToDevice, cs));
+  PDM_CHECK_CUDA(cudaMemcpyAsync(e->idx_dev, e->idx_host, (size_t)count * sizeof(int32_t), cudaMemcpyHostToDevice, cs));
   for (int64_t b = 0; b < nsteps; ++b) {
     const int n = (int)std::min<int64_t>(batch, count - b * batch);
     pdm_net_step_args a;
     memset(&a, 0, sizeof(a));
-    a.x = e->placed_images;
+    a.x = pl.images;
     a.x_dtype = PDM_U8;
-    a.y = e->placed_labels;
+    a.y = pl.labels;
     a.y_dtype = PDM_U8;
     a.row_index = e->idx_dev + b * batch;
     a.batch = n;
@@ -628,7 +714,7 @@ int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, 
     e->done_total += (uint32_t)pdm_net_planned_ctas(n, ctas);
   }
   PDM_CHECK_CUDA(cudaEventRecord(e->ev_end, cs));
-  PDM_CHECK_CUDA(cudaStreamSynchronize(cs));     // idx32 must outlive the upload
+  PDM_CHECK_CUDA(cudaStreamSynchronize(cs));
   if (device_ms) {
     float ms = 0.f;
     PDM_CHECK_CUDA(cudaEventElapsedTime(&ms, e->ev_begin, e->ev_end));
@@ -674,8 +760,9 @@ int pdm_engine_destroy(pdm_engine* e) {
   if (e->ev_begin) cudaEventDestroy(e->ev_begin);
   if (e->ev_end) cudaEventDestroy(e->ev_end);
   if (e->host_results) cudaFreeHost(e->host_results);
-  unplace_dataset(e);
+  unplace_all(e);
   if (e->idx_dev) cudaFree(e->idx_dev);
+  if (e->idx_host) cudaFreeHost(e->idx_host);
   if (e->scratch) cudaFree(e->scratch);
   if (e->sync) cudaFree(e->sync);
   if (e->metrics) cudaFree(e->metrics);

@@ -106,6 +106,7 @@ class MNISTDataLoader(object):
         # Optional fixed pass length (per process): a pass then walks as many successive epoch
         # permutations as needed.  Fixed-length "virtual epochs" for schedules and benchmarks.
         self.samples_per_epoch = samples_per_epoch
+        self._plan = None
 
         self.sampler = None
         if train and distributed_is_initialized():
@@ -119,6 +120,10 @@ class MNISTDataLoader(object):
     def set_sample_epoch(self, epoch=0):
         if self.train and self.sampler is not None:
             self.sampler.set_epoch(epoch)
+            # The epoch's index plan depends only on (seed, epoch): build it now, once, instead of
+            # inside the training pass (the permutation of 60,000 indices costs more than twenty
+            # fused steps).  ``epoch_indices()`` hands this plan out.
+            self._plan = (epoch, self._build_plan())
 
     @property
     def dataset(self):
@@ -142,6 +147,12 @@ class MNISTDataLoader(object):
 
     def epoch_indices(self):
         """The sample order for one pass, as an int64 tensor."""
+        plan = self._plan
+        if plan is not None and self.sampler is not None and plan[0] == self.sampler.epoch:
+            return plan[1]
+        return self._build_plan()
+
+    def _build_plan(self):
         if self.samples_per_epoch is None:
             return self._one_epoch()
         want = int(self.samples_per_epoch)

@@ -100,6 +100,8 @@ def _declare(lib):
                                    c_void_p, ctypes.POINTER(c_float)]
     lib.pdm_engine_run_device.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_int64, c_int, ctypes.c_int64,
                                           ctypes.POINTER(Hyper), c_int, ctypes.POINTER(c_float)]
+    lib.pdm_engine_run_device_typed.argtypes = [c_void_p, c_void_p, c_int, c_void_p, c_int, ctypes.c_int64, c_int,
+                                                ctypes.c_int64, ctypes.POINTER(Hyper), c_int, ctypes.POINTER(c_float)]
     lib.pdm_engine_metrics.argtypes = [c_void_p, ctypes.POINTER(ctypes.c_double), c_int]
     lib.pdm_engine_place_dataset.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_int64, c_int]
     lib.pdm_engine_run_gather.argtypes = [c_void_p, c_void_p, ctypes.c_int64, c_int, ctypes.POINTER(Hyper), c_int,

@@ -43,6 +43,7 @@ class NetEngine(object):
                                              flat.exp_avg_sq.data_ptr(), comm_h), 'pdm_engine_bind')
         self._dataset = None
         self._placed = None
+        self._keepalive = {}
         self.launches = 0       # kernels launched by this engine (bench bookkeeping)
 
     # -- dataset -------------------------------------------------------------
@@ -70,7 +71,9 @@ class NetEngine(object):
         ``'staged'``   (default) C++ loader threads gather each batch into pinned slots, one H2D copy per step
         ``'device'``   the whole set is copied to HBM once; the kernel gathers its rows itself
         ``'zerocopy'`` the host arrays are page-locked and mapped; the kernel gathers over PCIe
-        """
+
+        The native side keeps the last few placements, so coming back to a set that was placed before
+        (``Trainer`` switching between loaders) costs a table look-up, not another page-locking."""
         if placement == 'staged':
             self._placed = None
             return
@@ -82,6 +85,12 @@ class NetEngine(object):
         _lib.check(self._lib.pdm_engine_place_dataset(self._h, img.ctypes.data, lab.ctypes.data, img.shape[0],
                                                       self.PLACEMENTS[placement]), 'pdm_engine_place_dataset')
         self._placed = (key, placement)
+        self._keepalive[key] = (img, lab)       # a placement reads these arrays for as long as it is cached
+
+    def prepare(self, images_u8, labels_u8, placement):
+        """Everything a pass over this dataset needs that does not depend on the epoch."""
+        self.set_dataset(images_u8, labels_u8)
+        self.place_dataset(placement)
 
     # -- runs ------------------------------------------------------------------
     def _indices(self, indices):
@@ -126,14 +135,16 @@ class NetEngine(object):
         return float(ms.value)
 
     def train_device(self, dev_images, dev_labels, batch, nsteps, ctas=0):
-        """Training steps over a device-resident uint8 pool (kernel-only timing)."""
+        """Training steps over a device-resident pool (kernel-only timing).  ``dev_images`` is
+        [N, 784] uint8 (raw bytes, normalised in-kernel) or float32 (already normalised);
+        ``dev_labels`` [N] uint8 / int64 / int32."""
         ms = ctypes.c_float(0.0)
         h = self.optimizer.hyper(self.optimizer.step_count + 1)
         torch.cuda.current_stream(self.device).synchronize()
-        _lib.check(self._lib.pdm_engine_run_device(self._h, dev_images.data_ptr(), dev_labels.data_ptr(),
-                                                   int(dev_labels.numel()), int(batch), int(nsteps),
-                                                   ctypes.byref(h), int(ctas), ctypes.byref(ms)),
-                   'pdm_engine_run_device')
+        _lib.check(self._lib.pdm_engine_run_device_typed(
+            self._h, dev_images.data_ptr(), _lib.dtype_code(dev_images), dev_labels.data_ptr(),
+            _lib.dtype_code(dev_labels), int(dev_labels.numel()), int(batch), int(nsteps), ctypes.byref(h), int(ctas),
+            ctypes.byref(ms)), 'pdm_engine_run_device')
         self.optimizer.step_count += nsteps
         self.launches += nsteps
         if self.comm is not None and hasattr(self.comm, 'check_status'):

@@ -17,6 +17,7 @@ Two execution paths behind that surface:
 """
 from __future__ import annotations
 
+import numpy as np
 import torch
 
 from .data.loader import MNISTDataLoader
@@ -38,7 +39,7 @@ class Trainer(object):
                  loader_workers=None, data_placement='staged'):
         self.model = model
         self.optimizer = optimizer
-        self.train_loader = train_loader
+        self._train_loader = train_loader
         self.test_loader = test_loader
         self.device = torch.device(device)
         self.ctas = ctas
@@ -73,6 +74,24 @@ class Trainer(object):
         elif fused in (True, 'on'):
             raise RuntimeError('fused path requested but not available: needs a CUDA device, the native library, '
                                'the reference Net, a Fused optimizer and MNISTDataLoader inputs')
+        self._prepare_train_loader()
+
+    # The training loader is a property: binding one does the per-dataset set-up of the fused path
+    # (hand the arrays to the engine, page-lock / copy them for the in-kernel gather) right away, so
+    # that ``train()`` itself contains only per-epoch work -- like the reference, whose ``train()``
+    # has no hidden set-up cost either (ref:77-97).
+    @property
+    def train_loader(self):
+        return self._train_loader
+
+    @train_loader.setter
+    def train_loader(self, loader):
+        self._train_loader = loader
+        self._prepare_train_loader()
+
+    def _prepare_train_loader(self):
+        if self.engine is not None and isinstance(self._train_loader, MNISTDataLoader):
+            self.engine.prepare(self._train_loader.images, self._train_loader.labels, self.data_placement)
 
     def _fused_eligible(self):
         if self.device.type != 'cuda' or not torch.cuda.is_available():
@@ -127,17 +146,18 @@ class Trainer(object):
         train_acc = Accuracy()
         if self.engine is not None:
             loader = self.train_loader
-            self.engine.set_dataset(loader.images, loader.labels)
-            self.engine.place_dataset(self.data_placement)
+            self.engine.prepare(loader.images, loader.labels, self.data_placement)    # no-op unless the arrays changed
             idx = loader.epoch_indices()
             steps, ms = self.engine.train(idx, loader.batch_size, ctas=self.ctas)
             self.last_train_ms = ms
-            self.engine.metrics(reset=True)
-            n = idx.numel()
-            for i in range(steps.shape[0]):
-                b = min(loader.batch_size, n - i * loader.batch_size)
-                train_loss.update(float(steps[i, 0]), b)
-                train_acc.update_counts(int(round(float(steps[i, 1]))), b)
+            # fold the per-step {mean loss, correct} pairs the way the reference folds loss.item() and
+            # Accuracy.update (ref:94-95): sample-weighted, in float64, one vector operation
+            n, B = idx.numel(), loader.batch_size
+            sizes = np.full(steps.shape[0], B, dtype=np.float64)
+            if steps.shape[0]:
+                sizes[-1] = n - (steps.shape[0] - 1) * B
+            train_loss.update_sum(float(np.dot(steps[:, 0].astype(np.float64), sizes)), n)
+            train_acc.update_counts(int(np.rint(steps[:, 1]).sum()), n)
             return train_loss, train_acc
 
         if self.cnn_engine is not None:

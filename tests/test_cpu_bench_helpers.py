@@ -39,3 +39,18 @@ def test_bench_cli_contract():
     finally:
         sys.argv = argv
     assert called['gpus'] == 1 and called['steps'] == 5 and called['warmup'] == 3 and called['cnn'] is False
+
+
+def test_child_process_geometry(monkeypatch):
+    b = _bench()
+    monkeypatch.setenv('MASTER_PORT', '29611')
+    monkeypatch.setenv('TORCHELASTIC_USE_AGENT_STORE', 'True')
+    monkeypatch.setenv('GROUP_RANK', '0')
+    env = b.child_env(3, 3, 8, b.child_port(1))
+    assert env['RANK'] == '3' and env['LOCAL_RANK'] == '3' and env['WORLD_SIZE'] == '8'
+    assert env['MASTER_ADDR'] == '127.0.0.1' and 'GROUP_RANK' not in env
+    assert not any(k.startswith('TORCHELASTIC_') for k in env)
+    ports = {b.child_port(k) for k in (1, 2, 5)}
+    assert len(ports) == 3 and all(20000 <= p < 40000 and p != 29611 for p in ports)
+    # every rank derives the same port from the same parent rendezvous
+    assert b.child_port(2) == b.child_port(2)

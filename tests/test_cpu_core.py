@@ -260,3 +260,19 @@ def test_ddp_reports_parameters_without_gradient():
     model(x, use_b=False).sum().backward()      # head b gets no gradient
     with pytest.raises(RuntimeError, match='did not produce gradients for every parameter'):
         model(x)
+
+
+def test_epoch_plan_is_built_at_set_sample_epoch():
+    """set_sample_epoch (ref:231) prepares the epoch's index plan; train() only consumes it.  The plan handed
+    out must be exactly what the sampler yields for that epoch, and a stale plan is never used."""
+    from pytorch_distributed_mnist_b200.data.loader import MNISTDataLoader, ShardSampler
+    loader = MNISTDataLoader('unused', 32, train=True, synthetic=True, size=1000, samples_per_epoch=1500)
+    loader.sampler = ShardSampler(1000, num_replicas=2, rank=1)
+    loader.set_sample_epoch(3)
+    assert loader._plan is not None and loader._plan[0] == 3
+    got = loader.epoch_indices()
+    want = torch.cat([loader.sampler.indices(3), loader.sampler.indices(4), loader.sampler.indices(5)])[:1500]
+    assert torch.equal(got, want)
+    assert torch.equal(loader.epoch_indices(), want)          # asking twice in one epoch is fine
+    loader.sampler.set_epoch(7)                                # epoch moved behind the loader's back
+    assert torch.equal(loader.epoch_indices()[:500], loader.sampler.indices(7))
