@@ -173,6 +173,49 @@ int pdm_net_planned_ctas(int batch, int want_ctas);
 #define PDM_NET_STATIC_SCRATCH_BYTES (PDM_NET_STATIC_MAX_CTAS * PDM_NET_SCRATCH_STRIDE * 4)
 int pdm_net_train_step_static(const pdm_net_step_args* args, pdm_stream_t stream);
 
+/* The training loop of `Net` as ONE persistent kernel on the tensor cores (net_tc.cu): a cluster
+ * of PDM_TC_CLUSTER CTAs keeps the model (weights, optimizer moments) on chip and runs `nsteps`
+ * steps of ref:83-95 -- tcgen05.mma forward and weight-gradient GEMMs with TMEM accumulators,
+ * cross-CTA logit reduction through distributed shared memory, in-kernel LL all-reduce with the
+ * peers, Adam/SGD -- in a single launch.  Two input modes:
+ *   pool  (row_index == NULL) step i reads batch ((first_batch + i) mod (pool_rows / batch)) of x / y
+ *   plan  (row_index != NULL) step i reads rows row_index[i*batch ...] (last step ragged if count is
+ *         not a multiple of batch); x / y may be device memory or pinned, mapped host memory
+ *  x [rows,784] PDM_U8 raw pixels (normalised in-kernel), 16-byte aligned; y [rows] PDM_U8
+ *  params,m,v PDM_NET_FLAT floats, read at the start and written back after the last step
+ *  grad_out   optional PDM_NET_FLAT floats: the LAST step's reduced mean gradient
+ *  logits_out optional [batch,10]: the LAST step's logits (before the update)
+ *  step_out   optional [nsteps][2] {mean loss, #correct}, device or mapped host memory
+ *  metrics    optional 4 doubles, device: += {loss*B, correct, B, 0} per step
+ *  hyper.step 1-based index of the first update; peers.seq the LL sequence number of the first
+ *  step (the run consumes nsteps consecutive numbers).
+ * Math: raw pixels are exact in bf16; weights and dlogits enter the MMAs as three bf16 terms
+ * (hi + mid + lo), so products are exact and accumulation is fp32 -- fp32-faithful, not bf16.
+ * Softmax uses ex2.approx, the Adam update sqrt.approx / div.approx (<= 2 ulp each). */
+#define PDM_TC_CLUSTER 13
+typedef struct pdm_net_tc_args {
+  const uint8_t* x;
+  const uint8_t* y;
+  const int32_t* row_index;
+  int64_t pool_rows;
+  int64_t first_batch;
+  int64_t count;
+  int32_t batch;
+  int64_t nsteps;
+  float* params; float* m; float* v;
+  float* grad_out;
+  float* logits_out;
+  double* metrics;
+  float* step_out;
+  pdm_hyper hyper;
+  pdm_peers peers;
+} pdm_net_tc_args;
+/* 1 when `device` can launch the cluster kernel (compute capability 10.x, 13-CTA clusters). */
+int pdm_net_tc_supported(int device);
+int pdm_net_tc_run(const pdm_net_tc_args* args, pdm_stream_t stream);
+/* PDM_TC_TRACE=1 only: per-CTA clock stamps of the last run, [13][64][32] int64 (benchmarks/tc_trace.py). */
+int pdm_net_tc_trace_read(long long* out);
+
 /* Forward + loss + top-1 only (ref:106-114).  metrics (4 doubles, device) is
  * accumulated atomically: += {loss*B, correct, B, 0}.  Any grid size; no scratch. */
 int pdm_net_eval_step(const void* x, int x_dtype, const void* y, int y_dtype, int batch,

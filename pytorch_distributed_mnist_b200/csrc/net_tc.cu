@@ -1,0 +1,959 @@
+// net_tc.cu -- the reference model's training loop as ONE persistent thread-block-cluster kernel
+// on the 5th-generation tensor cores (tcgen05 / TMEM) of sm_100a.
+//
+// Reference path being replaced (ref:N = /root/reference/multi_proc_single_gpu.py), per step:
+//   ref:84-85 H2D copies, ref:87 addmm (K3), ref:88 cross_entropy (K4), ref:91 backward (K5-K7) +
+//   DDP reducer / ncclAllReduce (K8-K10), ref:92 Adam (K11), ref:94-95 metrics + 2 host syncs.
+// net_step.cu does one step per launch with FMA math, a grid barrier and a pass over per-CTA
+// partial gradients in L2.  This file removes the launch, the grid barrier and the partials:
+//
+//   * ONE launch runs `nsteps` steps.  A cluster of 13 CTAs owns the model: CTA c owns input
+//     columns [64c, 64c+64) (13 x 64 = 832 >= 784) -- their weights, Adam moments and gradient
+//     stay in registers / shared memory for the whole run and are written back at the end.
+//   * forward   P[512 x 48]    = X[512 x 64] . [W_hi; W_mid; W_lo]^T     tcgen05.mma kind::f16, M=128 N=48 K=16
+//     wgrad     G[64(+1) x 48] = X^T[64(+1) x 512] . [dl_hi | dl_mid | dl_lo]
+//     Both read the SAME shared-memory copy of the x tile: pixels are stored as bf16 (the integers
+//     0..255 are exact in bf16) in 8x8 core matrices without swizzle, which is a legal K-major
+//     operand (forward) and a legal MN-major operand (wgrad) at the same time.  fp32 operands
+//     (weights, dlogits) are split into three bf16 terms (hi + mid + lo = 24 mantissa bits) that
+//     sit side by side as three 16-column groups of ONE instruction, so every product is exact,
+//     accumulation is fp32 in TMEM, and the x tile is read from shared memory once per GEMM; the
+//     epilogues add the three groups.  The input normalisation (x/255 - mean)/std is folded into
+//     the epilogues.  A constant "ones" column appended to the tile makes the same wgrad MMA
+//     produce the bias gradient.
+//   * the K-split of the forward needs a cross-CTA reduction of the partial logits: every CTA owns
+//     40 rows of a 512-row block; partials travel as ONE bulk copy (cp.async.bulk shared::cta ->
+//     shared::cluster) per owner that completes a transaction mbarrier there -- no cluster barrier,
+//     no fence; the owner soft-maxes its rows and bulk-copies its rows of the wgrad operand
+//     (dlogits, already split) into every other CTA.
+//   * warp-specialised: 7 producer warps stream the NEXT step's rows (device memory, or pinned host
+//     memory over PCIe, optionally gathered through an index plan) while the current step computes;
+//     1 MMA-issuing warp; 4 epilogue/optimizer warps (TMEM lanes).
+//   * multi-GPU: the gradient of a CTA's columns is exchanged with the same CTA of every peer
+//     with the LL protocol of net_step.cu (8-byte {value, flag} units pushed over NVLink),
+//     summed in rank order (bit-identical replicas), inside the same kernel.
+#include "common.cuh"
+
+#include <math.h>
+#include <stdlib.h>
+
+namespace {
+
+constexpr int kCtas = PDM_TC_CLUSTER;        // 13
+constexpr int kCols = 64;                    // input columns per CTA
+constexpr int kIn = PDM_NET_IN;              // 784
+constexpr int kOut = PDM_NET_OUT;            // 10
+constexpr int kBlkRows = 512;                // rows per block (4 M-tiles of 128)
+constexpr int kOwnRows = 40;                 // rows of a block owned by one CTA (13 * 40 >= 512)
+constexpr int kThreads = 384;
+// Warp roles, lowest to highest warp id.  The SM's warp scheduler prefers the highest eligible warp id,
+// so the latency-critical epilogue/optimizer warps sit on top, then the MMA issuer, then the producers
+// (which mostly wait): measured 14.5 -> 9.4 us/step at batch 512 against the roles the other way round.
+constexpr int kProdThreads = 224;            // warps 0-6
+constexpr int kMmaWarp = 7;
+constexpr int kEpiThreads = 128;             // warps 8-11 (warp % 4 = TMEM lane quadrant)
+constexpr int kEpiFirst = 256;
+constexpr float kScale = 1.0f / (255.0f * 0.3081f);   // d(normalised x)/d(raw pixel)
+constexpr float kShift = 0.1307f / 0.3081f;           // mean / std
+
+// x tile: [row group (8 rows)][column block (8 cols)] core matrices of 128 bytes, 9 column blocks
+// per row group (8 real + the "ones" block), no swizzle.
+constexpr uint32_t kSc = 128;                // stride between column blocks
+constexpr uint32_t kColBlks = 9;
+constexpr uint32_t kSr = kColBlks * kSc;     // 1152: stride between row groups
+constexpr uint32_t kTileBytes = (kBlkRows / 8) * kSr;          // 73,728
+constexpr uint32_t kTilePad = 7 * kSc;       // M=128 wgrad reads 16 column blocks from the last row group
+constexpr uint32_t kDlSplitBytes = 2 * kBlkRows * 16;          // [n/8][row][n%8] bf16 = 16,384
+constexpr uint32_t kWopSplitBytes = 2 * 8 * 128;               // [n/8][k/8][n%8][k%8] bf16 = 2,048
+
+// shared memory map (bytes)
+constexpr uint32_t kOffTile = 0;
+constexpr uint32_t kOffDlop = kOffTile + kTileBytes + kTilePad;             // wgrad B operand: [split 3][n/8 2][row 512][8] bf16
+constexpr uint32_t kOffWop = kOffDlop + 3 * kDlSplitBytes;                  // forward B operand: [split 3][n/8 2][k/8 8][8][8] bf16
+constexpr uint32_t kOffXbuf = kOffWop + 3 * kWopSplitBytes;                 // partial logits of my rows from every CTA [13][40][10] f32
+constexpr uint32_t kXbufBytes = kCtas * kOwnRows * kOut * 4;                // 20,800
+constexpr uint32_t kOffStage = kOffXbuf + kXbufBytes;                       // my partial logits of all rows [512][10] f32 (bulk-copy source)
+constexpr uint32_t kStageBytes = kBlkRows * kOut * 4;                       // 20,480
+constexpr uint32_t kOffZbuf = kOffStage + kStageBytes;                      // summed logits of my rows [40][10] f32
+constexpr uint32_t kZbufBytes = kOwnRows * kOut * 4;                        // 1,600
+constexpr uint32_t kOffMisc = kOffZbuf + kZbufBytes;
+constexpr uint32_t kMiscBytes = 2048;
+constexpr uint32_t kOffTrace = kOffMisc + kMiscBytes;                       // [kTraceSteps][32] clock stamps (PDM_TC_TRACE=1)
+constexpr int kTraceSteps = 64;
+constexpr uint32_t kSmemBytes = kOffTrace + kTraceSteps * 32 * 8;
+constexpr uint32_t kTmemCols = 256;          // forward: 4 M-tiles x 48 columns, wgrad: 48 columns at column 192
+constexpr uint32_t kTmemWg = 192;
+
+struct Misc {                     // lives at kOffMisc
+  uint64_t bar_xfull, bar_fwd, bar_dl, bar_wg, bar_wop, bar_p1, bar_p2, bar_loss;
+  uint32_t tmem_slot;
+  uint32_t pad0;
+  float bias[16];
+  float wsum[2][16];              // per warp partial of sum_k W[n][k] over this CTA's columns
+  float db[16];
+  float adamc[2][4];              // by step parity: step_size, 1 / bc2_sqrt, first, unused
+  float lossw[2][2];              // per warp {loss, correct} of this CTA's rows of the current block
+  float lossbuf[kCtas][2];        // CTA 0: per-CTA {loss sum, correct}
+  uint8_t ys[kBlkRows];           // labels of the current block (written by the producers with the tile)
+};
+static_assert(sizeof(Misc) <= kMiscBytes, "Misc outgrew its slot");
+
+struct TcArgs {
+  const uint8_t* x;
+  const uint8_t* y;
+  const int32_t* row_index;
+  long long pool_batches;         // pool mode: batches in the pool
+  long long first_batch;
+  long long count;                // index mode: samples of the run
+  int batch;
+  long long nsteps;
+  float* params;
+  float* m;
+  float* v;
+  float* grad_out;
+  float* logits_out;
+  double* metrics;
+  float* step_out;
+  int opt;
+  float lr, beta1, beta2, eps, wd;
+  long long step0;                // 1-based index of the first update
+  float inv_world;
+  long long* trace;               // optional [13][kTraceSteps][32] clock64 stamps per CTA (PDM_TC_TRACE=1)
+  pdm_peers peers;
+};
+
+__device__ __forceinline__ long long clock_now() {
+  long long c;
+  asm volatile("mov.u64 %0, %%clock64;" : "=l"(c) :: "memory");     // the clobber pins the stamp between its neighbours
+  return c;
+}
+// stamps go to shared memory (a global store per stamp perturbs what it measures) and are dumped at the end
+#define TC_TRACE(cond, step, slot) do { if (a.trace != nullptr && (cond) && (step) < kTraceSteps) \
+    reinterpret_cast<long long*>(smem + kOffTrace)[(step) * 32 + (slot)] = clock_now(); } while (0)
+
+// ---------------------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t"
+      "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ uint32_t mapa(uint32_t local, uint32_t cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(cta));
+  return r;
+}
+// Store into another CTA's shared memory; the store's bytes complete a transaction on that CTA's mbarrier.
+__device__ __forceinline__ void st_async2(uint32_t raddr, float a, float b, uint32_t rbar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];"
+               ::"r"(raddr), "f"(a), "f"(b), "r"(rbar) : "memory");
+}
+// Bulk copy own shared memory -> another CTA's shared memory; ONE transaction on that CTA's mbarrier.
+__device__ __forceinline__ void bulk_s2s(uint32_t rdst, uint32_t src, uint32_t bytes, uint32_t rbar) {
+  asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(rdst), "r"(src), "r"(bytes), "r"(rbar) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+// 32 lanes x 16 consecutive columns: thread `lane` of warp w gets row 32*(w%4)+lane
+__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// UMMA shared-memory descriptor without swizzle (layout type 0), sm_100 version field = 1.
+//   K-major : LBO = stride between 8-element K chunks, SBO = stride between 8-row groups
+//   MN-major: SBO = stride between 8-element MN blocks, LBO = stride between 8-deep K groups
+// (both verified on hardware against an fp64 evaluation: tests/test_gpu_net_tc.py)
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
+// instruction descriptor: D = f32 (bits 4-5), A = B = bf16 (bits 7-9, 10-12), N >> 3 (17-22), M >> 4 (24-28)
+constexpr uint32_t kIdescBase = (1u << 4) | (1u << 7) | (1u << 10) | ((48u >> 3) << 17) | ((128u >> 4) << 24);
+constexpr uint32_t kIdescFwd = kIdescBase;                              // both operands K-major
+constexpr uint32_t kIdescWg = kIdescBase | (1u << 15) | (1u << 16);     // both operands MN-major
+
+__device__ __forceinline__ uint32_t bf16_bits(float f) {                // round-to-nearest-even
+  uint32_t u = __float_as_uint(f);
+  return (u + 0x7FFFu + ((u >> 16) & 1u)) >> 16;
+}
+__device__ __forceinline__ float bf16_val(uint32_t b) { return __uint_as_float(b << 16); }
+// f = hi + mid + lo with three bf16 terms (24 mantissa bits: exact for every fp32 in range)
+__device__ __forceinline__ void split3(float f, uint32_t& hi, uint32_t& mid, uint32_t& lo) {
+  hi = bf16_bits(f);
+  const float r1 = f - bf16_val(hi);
+  mid = bf16_bits(r1);
+  const float r2 = r1 - bf16_val(mid);
+  lo = bf16_bits(r2);
+}
+
+// inv_bc2 = 1 / sqrt(1 - beta2^t).  sqrt.approx / div.approx (<= 2 ulp): every rank runs the same
+// instructions on the same values, so replicas stay bit-identical.
+__device__ __forceinline__ void opt_update(int opt, float lr, float beta1, float beta2, float eps, float wd, float step_size,
+                                           float inv_bc2, bool first, float g, float& p, float& m, float& v) {
+  if (opt == PDM_OPT_ADAM) {
+    if (wd != 0.f) g = fmaf(wd, p, g);
+    m = m + (1.f - beta1) * (g - m);
+    v = v * beta2 + (1.f - beta2) * g * g;
+    float sq;
+    asm("sqrt.approx.f32 %0, %1;" : "=f"(sq) : "f"(v));
+    const float denom = fmaf(sq, inv_bc2, eps);
+    p = p - step_size * __fdividef(m, denom);
+  } else if (opt == PDM_OPT_SGD) {
+    if (wd != 0.f) g = fmaf(wd, p, g);
+    if (beta1 != 0.f) {
+      m = first ? g : (m * beta1 + g);
+      g = m;
+    }
+    p = p - lr * g;
+  }
+}
+
+// ---------------------------------------------------------------------------- work enumeration
+// A run is `nsteps` steps; a step of n rows is ceil(n / 512) blocks; every role walks the same
+// (step, block) sequence and numbers the blocks with one running counter (mbarrier parities).
+struct Blk {
+  int rows;        // valid rows of this block (1..512)
+  int tile_rows;   // rows rounded up to a multiple of 128 (rows the MMAs and the exchanges cover)
+  int n_step;      // rows of the whole step
+  bool first, last;
+};
+__device__ __forceinline__ int step_rows(const TcArgs& a, long long step) {
+  if (a.row_index == nullptr) return a.batch;
+  const long long left = a.count - step * (long long)a.batch;
+  return (int)(left < a.batch ? left : a.batch);
+}
+__device__ __forceinline__ Blk make_blk(int n_step, int blk) {
+  Blk b;
+  b.n_step = n_step;
+  const int left = n_step - blk * kBlkRows;
+  b.rows = left < kBlkRows ? left : kBlkRows;
+  b.tile_rows = (b.rows + 127) / 128 * 128;
+  b.first = blk == 0;
+  b.last = left <= kBlkRows;
+  return b;
+}
+// dataset row of local row r of (step, blk)
+__device__ __forceinline__ long long row_id(const TcArgs& a, long long step, int blk, int r) {
+  if (a.row_index != nullptr) return (long long)__ldg(a.row_index + step * (long long)a.batch + blk * kBlkRows + r);
+  return ((a.first_batch + step) % a.pool_batches) * (long long)a.batch + blk * kBlkRows + r;
+}
+
+__device__ __forceinline__ uint4 ld_stream16(const uint8_t* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+// four raw pixels -> four bf16 (exact), packed as two words.  No int->float conversion instruction
+// (quarter rate): 0x4B000000 | b is the float 8388608 + b, one full-rate FADD gives float(b), whose
+// upper 16 bits are its bf16.
+__device__ __forceinline__ void px4_to_bf16(uint32_t w, uint32_t& lo, uint32_t& hi) {
+  const float f0 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7540)) - 8388608.0f;
+  const float f1 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7541)) - 8388608.0f;
+  const float f2 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7542)) - 8388608.0f;
+  const float f3 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7543)) - 8388608.0f;
+  lo = __byte_perm(__float_as_uint(f0), __float_as_uint(f1), 0x7632);
+  hi = __byte_perm(__float_as_uint(f2), __float_as_uint(f3), 0x7632);
+}
+
+// Adam bias corrections of one step (same arithmetic as net_step.cu's host side, in double).
+__device__ __noinline__ void adam_consts(const TcArgs& a, long long step, float* out) {
+  const long long idx = a.step0 + step;
+  const double sidx = (double)(idx < 1 ? 1 : idx);
+  float step_size = 0.f, inv_bc2 = 1.f;
+  if (a.opt == PDM_OPT_ADAM) {
+    step_size = (float)((double)a.lr / (1.0 - pow((double)a.beta1, sidx)));
+    inv_bc2 = (float)(1.0 / sqrt(1.0 - pow((double)a.beta2, sidx)));
+  }
+  out[0] = step_size;
+  out[1] = inv_bc2;
+  out[2] = idx <= 1 ? 1.f : 0.f;
+}
+
+// ---------------------------------------------------------------------------- producer warps
+// 224 threads stream the rows (and labels) of the next block into registers while the current block
+// computes, then (once the wgrad MMAs of the current block have finished reading the tile) convert
+// them to bf16 and store them as 8x8 core matrices.
+__device__ __forceinline__ void producer_loop(const TcArgs& a, uint8_t* smem, Misc* ms, int pt, int cta) {
+  const int col0 = cta * kCols;
+  const int valid_cols = min(kCols, kIn - col0);
+  uint8_t* tile = smem + kOffTile;
+  uint32_t it = 0;
+  for (long long step = 0; step < a.nsteps; ++step) {
+    const int n_step = step_rows(a, step);
+    const int nblk = (n_step + kBlkRows - 1) / kBlkRows;
+    for (int blk = 0; blk < nblk; ++blk, ++it) {
+      const Blk b = make_blk(n_step, blk);
+      constexpr int kItems = (kBlkRows * 4 + kProdThreads - 1) / kProdThreads;   // 10
+      uint4 raw[kItems];
+#pragma unroll
+      for (int j = 0; j < kItems; ++j) {
+        const int item = pt + kProdThreads * j;
+        const int r = item >> 2, q = item & 3;
+        raw[j] = make_uint4(0u, 0u, 0u, 0u);
+        if (r < b.rows && q * 16 < valid_cols)
+          raw[j] = ld_stream16(a.x + row_id(a, step, blk, r) * kIn + col0 + q * 16);
+      }
+      uint32_t lab[3];                                         // labels travel with the tile (three rows per thread)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const int r = pt + kProdThreads * j;
+        lab[j] = 0u;
+        if (r < b.rows) lab[j] = min((uint32_t)__ldg(a.y + row_id(a, step, blk, r)), (uint32_t)(kOut - 1));
+      }
+      // one producer thread also prepares the step's Adam bias corrections (two double-precision pow):
+      // here it is off every critical path, the optimizer threads read it several barriers later
+      if (pt == 0 && blk == 0) adam_consts(a, step, ms->adamc[step & 1]);
+      TC_TRACE(pt == 32, step, 16);
+      if (it > 0) mbar_wait(&ms->bar_wg, (it - 1) & 1u);      // previous block's MMAs are done with the tile
+      TC_TRACE(pt == 32, step, 17);
+#pragma unroll
+      for (int j = 0; j < kItems; ++j) {
+        const int item = pt + kProdThreads * j;
+        const int r = item >> 2, q = item & 3;
+        if (r >= b.tile_rows) continue;
+        uint4 c0, c1;
+        px4_to_bf16(raw[j].x, c0.x, c0.y);
+        px4_to_bf16(raw[j].y, c0.z, c0.w);
+        px4_to_bf16(raw[j].z, c1.x, c1.y);
+        px4_to_bf16(raw[j].w, c1.z, c1.w);
+        uint8_t* dst = tile + (uint32_t)(r >> 3) * kSr + (uint32_t)(2 * q) * kSc + (uint32_t)(r & 7) * 16u;
+        *reinterpret_cast<uint4*>(dst) = c0;
+        *reinterpret_cast<uint4*>(dst + kSc) = c1;
+      }
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const int r = pt + kProdThreads * j;
+        if (r < kBlkRows) ms->ys[r] = (uint8_t)lab[j];
+      }
+      fence_async_smem();                                      // generic-proxy stores -> visible to the MMA (async proxy)
+      mbar_arrive(&ms->bar_xfull);
+      TC_TRACE(pt == 32, step, 18);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------- MMA warp (one lane)
+__device__ __forceinline__ void mma_loop(const TcArgs& a, uint8_t* smem, Misc* ms, uint32_t tmem_base) {
+  const uint32_t tile = smem_u32(smem + kOffTile), dlop = smem_u32(smem + kOffDlop), wop = smem_u32(smem + kOffWop);
+  uint32_t it = 0;
+  for (long long step = 0; step < a.nsteps; ++step) {
+    const int n_step = step_rows(a, step);
+    const int nblk = (n_step + kBlkRows - 1) / kBlkRows;
+    mbar_wait(&ms->bar_wop, (uint32_t)step & 1u);              // this step's weights are in the B operand
+    for (int blk = 0; blk < nblk; ++blk, ++it) {
+      const Blk b = make_blk(n_step, blk);
+      TC_TRACE(true, step, 8);
+      mbar_wait(&ms->bar_xfull, it & 1u);
+      tc_fence_after();
+      TC_TRACE(true, step, 9);
+      // ---- forward: [tile_rows x 48] = X[tile_rows x 64] . [W_hi; W_mid; W_lo]^T ----
+      const int ntiles = b.tile_rows / 128;
+      for (int mt = 0; mt < ntiles; ++mt) {
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+          const uint64_t da = make_desc(tile + (uint32_t)mt * 16u * kSr + (uint32_t)ks * 2u * kSc, kSc, kSr);
+          const uint64_t db = make_desc(wop + (uint32_t)ks * 256u, 128u, 1024u);     // 6 row groups of 8: [split][n / 8]
+          umma_bf16(tmem_base + (uint32_t)mt * 48u, da, db, kIdescFwd, ks != 0 ? 1u : 0u);
+        }
+      }
+      umma_commit(&ms->bar_fwd);
+      TC_TRACE(true, step, 10);
+      // ---- wgrad: G[(64 cols + ones + pad) x 48] (+)= X^T . [dl_hi | dl_mid | dl_lo] ----
+      mbar_wait(&ms->bar_dl, it & 1u);                        // this CTA's own rows of the operand (and the forward accumulator is drained)
+      mbar_wait(&ms->bar_p2, it & 1u);                        // the other CTAs' rows (bulk copies into the operand)
+      tc_fence_after();
+      TC_TRACE(true, step, 11);
+      const int ksteps = b.tile_rows / 16;
+      for (int ks = 0; ks < ksteps; ++ks) {
+        // MN-major, no swizzle: SBO = stride between 8-wide MN blocks, LBO = stride between 8-deep K groups
+        const uint64_t da = make_desc(tile + (uint32_t)ks * 2u * kSr, kSr, kSc);
+        const uint64_t db = make_desc(dlop + (uint32_t)ks * 256u, 128u, 8192u);      // 6 column blocks of 8: [split][n / 8]
+        umma_bf16(tmem_base + kTmemWg, da, db, kIdescWg, (!b.first || ks != 0) ? 1u : 0u);
+      }
+      umma_commit(&ms->bar_wg);
+      TC_TRACE(true, step, 12);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------- LL exchange with the peer GPUs
+// Thread t <= 64 of CTA c holds 10 gradient values (one input column, or the bias for t == 64).
+// They are pushed into every peer's inbox as 8-byte {value, flag} units and the peers' values are
+// polled from our own inbox; the sum is formed in rank order on every rank.  Two buffer halves
+// alternate by sequence parity (a rank can be at most one step ahead of any other).
+constexpr int kLLSlot = 65 * kOut;      // units per (parity, source rank, CTA)
+__device__ __forceinline__ void ll_exchange(const TcArgs& a, uint32_t seq, int cta, int t, float (&g)[kOut]) {
+  const int W = a.peers.world, me = a.peers.rank;
+  const size_t par = (size_t)(seq & 1u) * W;
+  for (int p = 0; p < W; ++p) {
+    if (p == me) continue;
+    uint64_t* dst = a.peers.inbox[p] + ((par + me) * kCtas + cta) * kLLSlot + (size_t)t * kOut;
+#pragma unroll
+    for (int i = 0; i < kOut; i += 2) ll_store2(dst + i, g[i], g[i + 1], seq);
+  }
+  float sum[kOut];
+#pragma unroll
+  for (int i = 0; i < kOut; ++i) sum[i] = 0.f;
+  for (int p = 0; p < W; ++p) {
+    if (p == me) {
+#pragma unroll
+      for (int i = 0; i < kOut; ++i) sum[i] += g[i];
+      continue;
+    }
+    const uint64_t* src = a.peers.inbox[me] + ((par + p) * kCtas + cta) * kLLSlot + (size_t)t * kOut;
+    float q[kOut];
+    uint32_t done = 0, spins = 0;
+    uint64_t t0 = 0;
+    while (done != 0x1Fu) {
+#pragma unroll
+      for (int i = 0; i < kOut; i += 2)
+        if (!((done >> (i / 2)) & 1u) && ll_load2(src + i, seq, q[i], q[i + 1])) done |= 1u << (i / 2);
+      if (done != 0x1Fu && (++spins & 1023u) == 0u && a.peers.timeout_ns != 0) {
+        const uint64_t now = globaltimer_ns();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > a.peers.timeout_ns) {
+          if (a.peers.status != nullptr) atomicExch(a.peers.status, 1 + p);
+          break;
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < kOut; ++i) sum[i] += q[i];
+  }
+#pragma unroll
+  for (int i = 0; i < kOut; ++i) g[i] = sum[i];
+}
+
+// Publish this thread's weights as the next forward's B operand (three bf16 terms, K-major 8x8
+// core matrices [split][n/8][k/8][n%8][k%8]) and its share of sum_k W[n][k].
+__device__ __forceinline__ void publish_weights(uint8_t* smem, Misc* ms, int t, int lane, int warp, const float (&p)[kOut]) {
+  uint8_t* wop = smem + kOffWop;
+  float s[kOut];
+#pragma unroll
+  for (int n = 0; n < kOut; ++n) {
+    uint32_t hi, mid, lo;
+    split3(p[n], hi, mid, lo);
+    const uint32_t off = (uint32_t)(n >> 3) * 1024u + (uint32_t)(t >> 3) * 128u + (uint32_t)(n & 7) * 16u + (uint32_t)(t & 7) * 2u;
+    *reinterpret_cast<uint16_t*>(wop + off) = (uint16_t)hi;
+    *reinterpret_cast<uint16_t*>(wop + kWopSplitBytes + off) = (uint16_t)mid;
+    *reinterpret_cast<uint16_t*>(wop + 2 * kWopSplitBytes + off) = (uint16_t)lo;
+    s[n] = p[n];
+  }
+  // ten independent butterfly reductions, level by level (the shuffles of one level overlap)
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+#pragma unroll
+    for (int n = 0; n < kOut; ++n) s[n] += __shfl_xor_sync(0xffffffffu, s[n], o);
+  }
+  if (lane < kOut) {
+    float mine = s[0];
+#pragma unroll
+    for (int n = 1; n < kOut; ++n) mine = lane == n ? s[n] : mine;
+    ms->wsum[warp][lane] = mine;
+  }
+}
+
+// ---------------------------------------------------------------------------- epilogue / optimizer warps
+__device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Misc* ms, uint32_t tmem_base, int t, int cta) {
+  const int warp = t >> 5, lane = t & 31;
+  const int col = cta * kCols + t;                       // input column of thread t < 64
+  const bool owns_col = t < kCols && col < kIn;
+  const bool is_bias = t == kCols;                       // thread 64 keeps a replica of the bias
+  float* xbuf = reinterpret_cast<float*>(smem + kOffXbuf);
+  float* stage = reinterpret_cast<float*>(smem + kOffStage);
+  float* zbuf = reinterpret_cast<float*>(smem + kOffZbuf);
+  uint8_t* dlop = smem + kOffDlop;
+  const uint32_t xbuf_s = smem_u32(xbuf), stage_s = smem_u32(stage), dlop_s = smem_u32(dlop);
+  const uint32_t p1_s = smem_u32(&ms->bar_p1), p2_s = smem_u32(&ms->bar_p2), loss_s = smem_u32(&ms->bar_loss);
+  const uint32_t lane_taddr = tmem_base + ((uint32_t)(warp * 32) << 16);
+  const int own_cap = min(kOwnRows, kBlkRows - cta * kOwnRows);
+
+  // ---- persistent per-thread state: this column's weights and optimizer moments ----
+  float p[kOut], m[kOut], v[kOut];
+#pragma unroll
+  for (int n = 0; n < kOut; ++n) {
+    p[n] = m[n] = v[n] = 0.f;
+    const int idx = is_bias ? kIn * kOut + n : n * kIn + col;
+    if (owns_col || is_bias) {
+      p[n] = a.params[idx];
+      if (a.m != nullptr) m[n] = a.m[idx];
+      if (a.v != nullptr) v[n] = a.v[idx];
+    }
+  }
+  if (t < kCols) publish_weights(smem, ms, t, lane, warp, p);
+  if (is_bias) {
+#pragma unroll
+    for (int n = 0; n < kOut; ++n) ms->bias[n] = p[n];
+  }
+  fence_async_smem();
+  mbar_arrive(&ms->bar_wop);                               // phase 0: the first step's weights
+  epi_sync();
+
+  float step_loss = 0.f, step_correct = 0.f;               // CTA 0, thread 0
+  uint32_t it = 0;
+  for (long long step = 0; step < a.nsteps; ++step) {
+    const int n_step = step_rows(a, step);
+    const int nblk = (n_step + kBlkRows - 1) / kBlkRows;
+    const float inv_batch = 1.0f / (float)n_step;
+    const bool last_step = step + 1 == a.nsteps;
+    float wsumn[kOut];
+#pragma unroll
+    for (int n = 0; n < kOut; ++n) wsumn[n] = kShift * (ms->wsum[0][n] + ms->wsum[1][n]);
+
+    for (int blk = 0; blk < nblk; ++blk, ++it) {
+      const Blk b = make_blk(n_step, blk);
+      const uint32_t par = it & 1u;
+      const int ntiles = b.tile_rows / 128;
+      const int my_rows = max(0, min(own_cap, b.tile_rows - cta * kOwnRows));
+      if (t == 0) {
+        mbar_expect_tx(&ms->bar_p1, (uint32_t)(kCtas * my_rows * kOut * 4));
+        mbar_expect_tx(&ms->bar_p2, (uint32_t)((b.tile_rows - my_rows) * 96));   // 6 x 16 bytes per remote row
+        if (cta == 0) mbar_expect_tx(&ms->bar_loss, (uint32_t)(kCtas * 8));
+      }
+
+      // ---- 1. partial logits of this CTA's 64 columns -> the rows' owners ----
+      TC_TRACE(t == 0, step, 0);
+      mbar_wait(&ms->bar_fwd, par);
+      tc_fence_after();
+      TC_TRACE(t == 0, step, 1);
+      // staged in shared memory, then ONE bulk copy per owner: rows [40 o, 40 o + 40) are contiguous
+      // and land in slot `cta` of owner o's exchange buffer
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt) {
+        if (mt >= ntiles) continue;
+        uint32_t hi[16], mid[16], lo[16];
+        tmem_ld16_issue(lane_taddr + (uint32_t)mt * 48u, hi);
+        tmem_ld16_issue(lane_taddr + (uint32_t)mt * 48u + 16u, mid);
+        tmem_ld16_issue(lane_taddr + (uint32_t)mt * 48u + 32u, lo);
+        tmem_ld_wait();
+        float2* dst = reinterpret_cast<float2*>(stage + (mt * 128 + t) * kOut);
+#pragma unroll
+        for (int n = 0; n < kOut; n += 2) {
+          const float z0 = (__uint_as_float(hi[n]) + __uint_as_float(mid[n])) + __uint_as_float(lo[n]);
+          const float z1 = (__uint_as_float(hi[n + 1]) + __uint_as_float(mid[n + 1])) + __uint_as_float(lo[n + 1]);
+          dst[n / 2] = make_float2(fmaf(kScale, z0, -wsumn[n]), fmaf(kScale, z1, -wsumn[n + 1]));
+        }
+      }
+      fence_async_smem();
+      epi_sync();
+      if (t < kCtas) {
+        const int rows_o = max(0, min(min(kOwnRows, kBlkRows - t * kOwnRows), b.tile_rows - t * kOwnRows));
+        if (rows_o > 0)
+          bulk_s2s(mapa(xbuf_s + (uint32_t)(cta * kOwnRows * kOut) * 4u, (uint32_t)t), stage_s + (uint32_t)(t * kOwnRows * kOut) * 4u,
+                   (uint32_t)(rows_o * kOut * 4), mapa(p1_s, (uint32_t)t));
+      }
+      mbar_wait(&ms->bar_xfull, par);          // (long complete) acquire the producers' label stores
+
+      // ---- 2. owner: sum the 13 partials (all threads), then one thread per row: soft-max, loss,
+      //         top-1, dlogits as three bf16 terms straight into the wgrad operand ----
+      TC_TRACE(t == 0, step, 2);
+      mbar_wait(&ms->bar_p1, par);
+      TC_TRACE(t == 0, step, 3);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int i = t + kEpiThreads * j;
+        if (i < my_rows * kOut) {
+          const int c = i % kOut;
+          float z = ms->bias[c];
+#pragma unroll
+          for (int src = 0; src < kCtas; ++src) z += xbuf[src * kOwnRows * kOut + i];
+          zbuf[i] = z;
+        }
+      }
+      epi_sync();
+      float my_loss = 0.f, my_hit = 0.f;
+      if (t < my_rows) {
+        const int r = cta * kOwnRows + t;
+        const bool valid = r < b.rows;
+        float z[kOut];
+#pragma unroll
+        for (int n = 0; n < kOut; n += 2) {
+          const float2 zz = *reinterpret_cast<const float2*>(zbuf + t * kOut + n);
+          z[n] = zz.x;
+          z[n + 1] = zz.y;
+        }
+        const int y = (int)ms->ys[r];
+        float mx = z[0];
+#pragma unroll
+        for (int n = 1; n < kOut; ++n) mx = fmaxf(mx, z[n]);
+        float e[kOut], s = 0.f, zy = z[0];
+        bool hit = true;
+#pragma unroll
+        for (int n = 0; n < kOut; ++n) {
+          e[n] = __expf(z[n] - mx);                          // ex2.approx: <= 2e-6 relative on the probabilities
+          s += e[n];
+          zy = n == y ? z[n] : zy;
+        }
+#pragma unroll
+        for (int n = 0; n < kOut; ++n) hit = hit && !(z[n] > zy || (z[n] == zy && n < y));
+        const float inv_s = __fdividef(1.0f, s);
+        uint32_t hi[kOut], mid[kOut], lo[kOut];
+#pragma unroll
+        for (int n = 0; n < kOut; ++n) {
+          const float d = valid ? (e[n] * inv_s - (n == y ? 1.f : 0.f)) * inv_batch : 0.f;
+          split3(d, hi[n], mid[n], lo[n]);
+          if (a.logits_out != nullptr && last_step && valid) a.logits_out[(size_t)(blk * kBlkRows + r) * kOut + n] = z[n];
+        }
+        // wgrad B operand, MN-major 8x8 core matrices: [split][n / 8][row][n % 8] bf16
+        const uint32_t off = (uint32_t)r * 16u;
+        *reinterpret_cast<uint4*>(dlop + off) =
+            make_uint4(hi[0] | (hi[1] << 16), hi[2] | (hi[3] << 16), hi[4] | (hi[5] << 16), hi[6] | (hi[7] << 16));
+        *reinterpret_cast<uint4*>(dlop + 8192u + off) = make_uint4(hi[8] | (hi[9] << 16), 0u, 0u, 0u);
+        *reinterpret_cast<uint4*>(dlop + kDlSplitBytes + off) =
+            make_uint4(mid[0] | (mid[1] << 16), mid[2] | (mid[3] << 16), mid[4] | (mid[5] << 16), mid[6] | (mid[7] << 16));
+        *reinterpret_cast<uint4*>(dlop + kDlSplitBytes + 8192u + off) = make_uint4(mid[8] | (mid[9] << 16), 0u, 0u, 0u);
+        *reinterpret_cast<uint4*>(dlop + 2 * kDlSplitBytes + off) =
+            make_uint4(lo[0] | (lo[1] << 16), lo[2] | (lo[3] << 16), lo[4] | (lo[5] << 16), lo[6] | (lo[7] << 16));
+        *reinterpret_cast<uint4*>(dlop + 2 * kDlSplitBytes + 8192u + off) = make_uint4(lo[8] | (lo[9] << 16), 0u, 0u, 0u);
+        if (valid) {
+          my_loss = (mx + logf(s)) - zy;
+          my_hit = hit ? 1.f : 0.f;
+        }
+      }
+      if (warp < 2) {                                        // rows 0-31 and 32-39: fixed butterfly, deterministic
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+          my_loss += __shfl_xor_sync(0xffffffffu, my_loss, o);
+          my_hit += __shfl_xor_sync(0xffffffffu, my_hit, o);
+        }
+        if (lane == 0) { ms->lossw[warp][0] = my_loss; ms->lossw[warp][1] = my_hit; }
+      }
+      fence_async_smem();
+      epi_sync();
+      // my rows of the operand -> the same rows of every other CTA's operand: 6 chunks (split, n / 8)
+      // of my_rows x 16 bytes per destination, one transaction each
+      if (t < 6 * (kCtas - 1) && my_rows > 0) {
+        const int dsel = t / 6, chunk = t - dsel * 6;
+        const uint32_t dest = (uint32_t)(dsel + (dsel >= cta ? 1 : 0));
+        const uint32_t off = (uint32_t)chunk * 8192u + (uint32_t)(cta * kOwnRows) * 16u;
+        bulk_s2s(mapa(dlop_s + off, dest), dlop_s + off, (uint32_t)my_rows * 16u, mapa(p2_s, dest));
+      }
+      if (t == 0)
+        st_async2(mapa(smem_u32(&ms->lossbuf[cta][0]), 0u), ms->lossw[0][0] + ms->lossw[1][0], ms->lossw[0][1] + ms->lossw[1][1],
+                  mapa(loss_s, 0u));
+      tc_fence_before();
+      mbar_arrive(&ms->bar_dl);                              // own rows written, forward accumulator drained
+      TC_TRACE(t == 0, step, 4);
+
+      if (cta == 0 && t == 0) {                              // the step's metrics
+        mbar_wait(&ms->bar_loss, par);
+        for (int i = 0; i < kCtas; ++i) { step_loss += ms->lossbuf[i][0]; step_correct += ms->lossbuf[i][1]; }
+        if (b.last) {
+          if (a.step_out != nullptr) {
+            a.step_out[2 * step] = step_loss * inv_batch;
+            a.step_out[2 * step + 1] = step_correct;
+          }
+          if (a.metrics != nullptr) {
+            a.metrics[0] += (double)step_loss;
+            a.metrics[1] += (double)step_correct;
+            a.metrics[2] += (double)n_step;
+          }
+          step_loss = step_correct = 0.f;
+        }
+      }
+
+      // ---- 3. gradient of this CTA's columns, all-reduce, optimizer, next step's B operand ----
+      TC_TRACE(t == 0, step, 6);
+      mbar_wait(&ms->bar_wg, par);
+      TC_TRACE(t == 0, step, 7);
+      if (!b.last) continue;
+      tc_fence_after();
+      float gsum[kOut];
+      {
+        uint32_t hi[16], mid[16], lo[16];
+        tmem_ld16_issue(lane_taddr + kTmemWg, hi);
+        tmem_ld16_issue(lane_taddr + kTmemWg + 16u, mid);
+        tmem_ld16_issue(lane_taddr + kTmemWg + 32u, lo);
+        tmem_ld_wait();
+#pragma unroll
+        for (int n = 0; n < kOut; ++n) gsum[n] = (__uint_as_float(hi[n]) + __uint_as_float(mid[n])) + __uint_as_float(lo[n]);
+      }
+      if (is_bias) {
+#pragma unroll
+        for (int n = 0; n < kOut; ++n) ms->db[n] = gsum[n];
+      }
+      epi_sync();
+      TC_TRACE(t == 0, step, 21);
+      if (t <= kCols) {
+        float g[kOut];
+#pragma unroll
+        for (int n = 0; n < kOut; ++n) {
+          const float dbn = ms->db[n];
+          g[n] = is_bias ? dbn : (owns_col ? fmaf(kScale, gsum[n], -kShift * dbn) : 0.f);
+        }
+        if (a.peers.world > 1) ll_exchange(a, a.peers.seq + (uint32_t)step, cta, t, g);
+        const float* ac = ms->adamc[step & 1];
+        const float step_size = ac[0], inv_bc2 = ac[1];
+        const bool first = ac[2] != 0.f;
+        if (owns_col || is_bias) {
+#pragma unroll
+          for (int n = 0; n < kOut; ++n) {
+            g[n] *= a.inv_world;
+            opt_update(a.opt, a.lr, a.beta1, a.beta2, a.eps, a.wd, step_size, inv_bc2, first, g[n], p[n], m[n], v[n]);
+          }
+          if (owns_col || cta == 0) {
+#pragma unroll
+            for (int n = 0; n < kOut; ++n) {
+              const int idx = is_bias ? kIn * kOut + n : n * kIn + col;
+              if (a.grad_out != nullptr) a.grad_out[idx] = g[n];
+              if (last_step) {
+                a.params[idx] = p[n];
+                if (a.m != nullptr) a.m[idx] = m[n];
+                if (a.v != nullptr) a.v[idx] = v[n];
+              }
+            }
+          }
+        }
+        TC_TRACE(t == 0, step, 22);
+        if (t < kCols) publish_weights(smem, ms, t, lane, warp, p);
+        if (is_bias) {
+#pragma unroll
+          for (int n = 0; n < kOut; ++n) ms->bias[n] = p[n];
+        }
+      }
+      TC_TRACE(t == 0, step, 23);
+      fence_async_smem();
+      tc_fence_before();
+      mbar_arrive(&ms->bar_wop);
+      epi_sync();
+      TC_TRACE(t == 0, step, 13);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------- the kernel
+__global__ void __launch_bounds__(kThreads, 1) net_tc_kernel(const __grid_constant__ TcArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  Misc* ms = reinterpret_cast<Misc*>(smem + kOffMisc);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  uint32_t cta;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta));
+
+  // zero every operand buffer (padding rows / columns must hold finite values), then the ones column
+  for (uint32_t i = tid; i < kSmemBytes / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0u, 0u, 0u, 0u);
+  __syncthreads();
+  for (int r = tid; r < kBlkRows; r += kThreads)
+    *reinterpret_cast<uint16_t*>(smem + kOffTile + (uint32_t)(r >> 3) * kSr + 8u * kSc + (uint32_t)(r & 7) * 16u) = 0x3F80;  // bf16 1.0
+  if (tid == 0) {
+    mbar_init(&ms->bar_xfull, kProdThreads);
+    mbar_init(&ms->bar_fwd, 1);
+    mbar_init(&ms->bar_dl, kEpiThreads);
+    mbar_init(&ms->bar_wg, 1);
+    mbar_init(&ms->bar_wop, kEpiThreads);
+    mbar_init(&ms->bar_p1, 1);
+    mbar_init(&ms->bar_p2, 1);
+    mbar_init(&ms->bar_loss, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kMmaWarp) tmem_alloc(&ms->tmem_slot, kTmemCols);
+  fence_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  cluster_sync_all();                     // every CTA's mbarriers exist before anyone copies to them
+  const uint32_t tmem_base = ms->tmem_slot;
+
+  if (tid >= kEpiFirst) {
+    epilogue_loop(a, smem, ms, tmem_base, tid - kEpiFirst, (int)cta);
+  } else if (warp == kMmaWarp) {
+    if ((tid & 31) == 0) mma_loop(a, smem, ms, tmem_base);
+    __syncwarp();
+  } else {
+    producer_loop(a, smem, ms, tid, (int)cta);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (a.trace != nullptr)
+    for (int i = tid; i < kTraceSteps * 32; i += kThreads)
+      a.trace[(size_t)cta * kTraceSteps * 32 + i] = reinterpret_cast<const long long*>(smem + kOffTrace)[i];
+  cluster_sync_all();                     // no CTA leaves while a peer may still address its shared memory
+  if (warp == kMmaWarp) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------- host side
+static void tc_launch_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, cudaStream_t stream) {
+  *cfg = cudaLaunchConfig_t{};
+  cfg->gridDim = dim3(kCtas);
+  cfg->blockDim = dim3(kThreads);
+  cfg->dynamicSmemBytes = kSmemBytes;
+  cfg->stream = stream;
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kCtas;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg->attrs = attr;
+  cfg->numAttrs = 1;
+}
+
+extern "C" int pdm_net_tc_supported(int device) {
+  static int cached[64];
+  static bool known[64];
+  if (device < 0 || device >= 64) return 0;
+  if (known[device]) return cached[device];
+  int ok = 0;
+  do {
+    const char* e = getenv("PDM_NET_TC");
+    if (e && *e == '0') break;
+    int cur = -1;
+    if (cudaGetDevice(&cur) != cudaSuccess) break;
+    if (cur != device && cudaSetDevice(device) != cudaSuccess) break;
+    int major = 0, cluster = 0;
+    cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
+    cudaDeviceGetAttribute(&cluster, cudaDevAttrClusterLaunch, device);
+    if (major == 10 && cluster) {
+      if (cudaFuncSetAttribute(net_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes) == cudaSuccess &&
+          cudaFuncSetAttribute(net_tc_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
+        cudaLaunchConfig_t cfg;
+        cudaLaunchAttribute attr[1];
+        tc_launch_config(&cfg, attr, nullptr);
+        int nclusters = 0;
+        if (cudaOccupancyMaxActiveClusters(&nclusters, net_tc_kernel, &cfg) == cudaSuccess && nclusters >= 1) ok = 1;
+      }
+    }
+    cudaGetLastError();
+    if (cur != device && cur >= 0) cudaSetDevice(cur);
+  } while (0);
+  cached[device] = ok;
+  known[device] = true;
+  return ok;
+}
+
+// PDM_TC_TRACE=1: every CTA stamps clock64 at its synchronisation points for the first 64 steps of
+// a run (profiling aid, benchmarks/tc_trace.py); pdm_net_tc_trace_read copies the stamps out.
+static long long* g_tc_trace = nullptr;
+static long long* tc_trace_buffer() {
+  static const bool on = [] { const char* e = getenv("PDM_TC_TRACE"); return e && *e == '1'; }();
+  if (!on) return nullptr;
+  const size_t bytes = (size_t)kCtas * kTraceSteps * 32 * sizeof(long long);
+  if (g_tc_trace == nullptr && cudaMalloc((void**)&g_tc_trace, bytes) != cudaSuccess) return nullptr;
+  cudaMemset(g_tc_trace, 0, bytes);
+  return g_tc_trace;
+}
+extern "C" int pdm_net_tc_trace_read(long long* out) {
+  PDM_REQUIRE(out != nullptr, PDM_ERR_ARG, "pdm_net_tc_trace_read: out is NULL");
+  PDM_REQUIRE(g_tc_trace != nullptr, PDM_ERR_STATE, "pdm_net_tc_trace_read: tracing is off (set PDM_TC_TRACE=1)");
+  PDM_CHECK_CUDA(cudaDeviceSynchronize());
+  PDM_CHECK_CUDA(cudaMemcpy(out, g_tc_trace, (size_t)kCtas * kTraceSteps * 32 * sizeof(long long), cudaMemcpyDeviceToHost));
+  return PDM_OK;
+}
+
+extern "C" int pdm_net_tc_run(const pdm_net_tc_args* g, pdm_stream_t stream) {
+  PDM_REQUIRE(g != nullptr, PDM_ERR_ARG, "pdm_net_tc_run: args is NULL");
+  PDM_REQUIRE(g->x && g->y && g->params, PDM_ERR_ARG, "pdm_net_tc_run: x, y and params are required");
+  PDM_REQUIRE(((uintptr_t)g->x & 15) == 0, PDM_ERR_ARG, "pdm_net_tc_run: x must be 16-byte aligned");
+  PDM_REQUIRE(g->batch >= 1, PDM_ERR_ARG, "pdm_net_tc_run: batch must be >= 1 (got %d)", g->batch);
+  PDM_REQUIRE(g->nsteps >= 0, PDM_ERR_ARG, "pdm_net_tc_run: nsteps must be >= 0");
+  const pdm_hyper& h = g->hyper;
+  PDM_REQUIRE(h.opt == PDM_OPT_ADAM || h.opt == PDM_OPT_SGD || h.opt == PDM_OPT_NONE, PDM_ERR_ARG,
+              "pdm_net_tc_run: unknown optimizer %d", h.opt);
+  PDM_REQUIRE(h.opt != PDM_OPT_ADAM || (g->m && g->v), PDM_ERR_ARG, "pdm_net_tc_run: Adam needs m and v");
+  PDM_REQUIRE(!(h.opt == PDM_OPT_SGD && h.beta1 != 0.f) || g->m, PDM_ERR_ARG, "pdm_net_tc_run: SGD with momentum needs m");
+  TcArgs a;
+  memset(&a, 0, sizeof(a));
+  long long nsteps = g->nsteps;
+  if (g->row_index != nullptr) {
+    PDM_REQUIRE(g->count >= 0, PDM_ERR_ARG, "pdm_net_tc_run: count must be >= 0");
+    const long long need = (g->count + g->batch - 1) / g->batch;
+    if (nsteps == 0 || nsteps > need) nsteps = need;
+    a.count = g->count;
+  } else {
+    PDM_REQUIRE(g->pool_rows >= g->batch, PDM_ERR_ARG, "pdm_net_tc_run: the pool holds fewer rows than one batch");
+    a.pool_batches = g->pool_rows / g->batch;
+    a.first_batch = g->first_batch % a.pool_batches;
+  }
+  if (nsteps == 0) return PDM_OK;
+  const int world = g->peers.world > 1 ? g->peers.world : 1;
+  PDM_REQUIRE(world <= PDM_MAX_RANKS, PDM_ERR_LIMIT, "pdm_net_tc_run: world %d > %d", world, PDM_MAX_RANKS);
+  if (world > 1) {
+    PDM_REQUIRE(g->peers.seq != 0, PDM_ERR_ARG, "pdm_net_tc_run: peers.seq must be non-zero");
+    PDM_REQUIRE(g->peers.rank >= 0 && g->peers.rank < world, PDM_ERR_ARG, "pdm_net_tc_run: bad rank");
+    for (int p = 0; p < world; ++p)
+      PDM_REQUIRE(g->peers.inbox[p] != nullptr, PDM_ERR_STATE, "pdm_net_tc_run: inbox[%d] not mapped", p);
+  }
+  int dev = 0;
+  PDM_CHECK_CUDA(cudaGetDevice(&dev));
+  PDM_REQUIRE(pdm_net_tc_supported(dev) == 1, PDM_ERR_STATE,
+              "pdm_net_tc_run: device %d cannot launch a %d-CTA cluster with %u bytes of shared memory per CTA "
+              "(or PDM_NET_TC=0)", dev, kCtas, kSmemBytes);
+  a.x = g->x;
+  a.y = g->y;
+  a.row_index = g->row_index;
+  a.batch = g->batch;
+  a.nsteps = nsteps;
+  a.params = g->params;
+  a.m = g->m;
+  a.v = g->v;
+  a.grad_out = g->grad_out;
+  a.logits_out = g->logits_out;
+  a.metrics = g->metrics;
+  a.step_out = g->step_out;
+  a.opt = h.opt;
+  a.lr = h.lr; a.beta1 = h.beta1; a.beta2 = h.beta2; a.eps = h.eps; a.wd = h.weight_decay;
+  a.step0 = h.step;
+  a.inv_world = world > 1 ? 1.0f / (float)world : 1.0f;
+  a.trace = tc_trace_buffer();
+  a.peers = g->peers;
+  a.peers.world = world;
+
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr[1];
+  tc_launch_config(&cfg, attr, (cudaStream_t)stream);
+  void* params[] = {&a};
+  PDM_CHECK_CUDA(cudaLaunchKernelExC(&cfg, (const void*)net_tc_kernel, params));
+  return PDM_OK;
+}
