@@ -361,6 +361,7 @@ void* pdm_comm_data(pdm_comm* c);                              /* local data are
 size_t pdm_comm_data_bytes(pdm_comm* c);
 int pdm_comm_set_timeout(pdm_comm* c, double seconds);         /* 0 = wait forever; default 30 s */
 int pdm_comm_peers(pdm_comm* c, pdm_peers* out, int advance);  /* links for pdm_net_train_step */
+int pdm_comm_peers_block(pdm_comm* c, pdm_peers* out, int64_t nsteps); /* links + nsteps sequence numbers (pdm_net_tc_run) */
 int pdm_comm_status(pdm_comm* c, int* status);                 /* 0, or 1 + rank that timed out */
 int pdm_comm_barrier(pdm_comm* c, pdm_stream_t stream);
 /* Every rank ends up with root's bytes [offset, offset+bytes) (DDP's initial
@@ -435,7 +436,9 @@ int pdm_engine_set_dataset(pdm_engine* e, const uint8_t* images, const uint8_t* 
  * step_results (host, [nsteps][2]) gets {mean loss, correct} per step.  Blocks until done. */
 int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int batch, int train,
                    const pdm_hyper* hyper, int ctas, float* step_results, float* device_ms);
-/* nsteps training steps over a device-resident pool of samples; no host traffic. */
+/* nsteps training steps over a device-resident pool of samples; no host traffic.  With raw uint8
+ * inputs and ctas == 0 the pass is ONE launch of the persistent tensor-core kernel (pdm_net_tc_run)
+ * on devices that support it (PDM_NET_TC=0 disables); the same holds for pdm_engine_run_gather. */
 int pdm_engine_run_device(pdm_engine* e, const uint8_t* dev_images, const uint8_t* dev_labels,
                           int64_t pool_samples, int batch, int64_t nsteps, const pdm_hyper* hyper,
                           int ctas, float* device_ms);
@@ -452,6 +455,8 @@ int pdm_engine_place_dataset(pdm_engine* e, const uint8_t* images, const uint8_t
 int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, int batch,
                           const pdm_hyper* hyper, int ctas, float* step_results, float* device_ms);
 int pdm_engine_metrics(pdm_engine* e, double out[4], int reset);
+/* Kernels launched by the last pdm_engine_run* call (1 when the persistent tensor-core kernel took the pass). */
+int64_t pdm_engine_last_launches(pdm_engine* e);
 void* pdm_engine_scratch(pdm_engine* e);
 void* pdm_engine_sync_words(pdm_engine* e);
 void* pdm_engine_metrics_ptr(pdm_engine* e);

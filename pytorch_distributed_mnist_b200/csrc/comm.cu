@@ -39,7 +39,7 @@
 
 namespace {
 
-constexpr size_t kLLBytes = 1u << 20;  // >= 2 * 8 * 1963 * 32
+constexpr size_t kLLBytes = 2u << 20;  // >= 2 * 8 * 1963 * 32 (net_step.cu) and >= 2 * 8 * 13 * 650 * 8 (net_tc.cu)
 constexpr size_t kFlagBytes = 4096;
 constexpr size_t kHeaderBytes = kLLBytes + kFlagBytes;
 constexpr int kFlagStart = 0;   // word offsets inside the flag block (32 words = 128 B apart)
@@ -338,6 +338,20 @@ int pdm_comm_peers(pdm_comm* c, pdm_peers* out, int advance) {
   for (int p = 0; p < c->world; ++p) out->inbox[p] = reinterpret_cast<uint64_t*>(c->base[p]);
   out->status = reinterpret_cast<int32_t*>(reinterpret_cast<uint32_t*>(c->local + kLLBytes) + kFlagStatus);
   out->timeout_ns = c->timeout_ns;
+  return PDM_OK;
+}
+
+// Peer links for a persistent multi-step kernel (net_tc.cu): reserves `nsteps` consecutive LL sequence
+// numbers; out->seq is the first of them.
+int pdm_comm_peers_block(pdm_comm* c, pdm_peers* out, int64_t nsteps) {
+  PDM_REQUIRE(nsteps >= 1, PDM_ERR_ARG, "pdm_comm_peers_block: nsteps must be >= 1");
+  int rc = pdm_comm_peers(c, out, 1);
+  if (rc != PDM_OK) return rc;
+  c->ll_seq += (uint32_t)(nsteps - 1);
+  if (c->ll_seq < out->seq) {            // wrapped past zero inside the block: start the block after the wrap
+    c->ll_seq = 0;
+    return pdm_comm_peers_block(c, out, nsteps);
+  }
   return PDM_OK;
 }
 

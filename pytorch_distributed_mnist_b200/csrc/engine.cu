@@ -31,6 +31,7 @@
 #include <vector>
 
 extern "C" int pdm_comm_peers(struct pdm_comm* c, pdm_peers* out, int advance);
+extern "C" int pdm_comm_peers_block(struct pdm_comm* c, pdm_peers* out, int64_t nsteps);
 
 namespace {
 
@@ -88,6 +89,7 @@ struct pdm_engine {
   double* metrics = nullptr;
   float* step_out = nullptr;              // [slots][2]
   uint32_t done_total = 0;                // CTAs launched so far on `sync` (step-to-step flag dependency)
+  int64_t last_launches = 0;              // kernels launched by the last run_* call
   std::vector<uint8_t*> dev_slot;         // [slots] packed batch
   std::vector<uint8_t*> host_slot;        // [slots] pinned staging
   float* host_results = nullptr;          // pinned + mapped [capacity][2]
@@ -208,6 +210,12 @@ void worker_main(pdm_engine* e) {
     }
     e->cv_filled.notify_all();
   }
+}
+
+// The persistent tensor-core kernel (net_tc.cu) takes a whole pass in one launch: used for raw uint8
+// inputs whenever the device can launch it and the caller did not ask for a specific CTA count.
+bool use_tc(const pdm_engine* e, int x_dtype, int y_dtype, int ctas) {
+  return x_dtype == PDM_U8 && y_dtype == PDM_U8 && ctas == 0 && pdm_net_tc_supported(e->device) == 1;
 }
 
 int ensure_results(pdm_engine* e, int64_t nsteps) {
@@ -340,6 +348,7 @@ int pdm_engine_run(pdm_engine* e, const int64_t* indices, int64_t count, int bat
     for (int s = 0; s < e->slots; ++s) { e->filled_batch[s] = -1; e->free_for[s] = s; }
     e->job_id += 1;
   }
+  e->last_launches = nsteps;
   DBG("run: %lld steps of batch %d (train=%d)", (long long)nsteps, batch, train);
   e->cv_work.notify_all();
 
@@ -503,6 +512,35 @@ int pdm_engine_run_device_typed(pdm_engine* e, const void* dev_images, int x_dty
   PDM_CHECK_CUDA(cudaSetDevice(e->device));
   const int64_t nb = pool_samples / batch;
   cudaStream_t st = e->stream[0];
+  if (nsteps >= 1 && use_tc(e, x_dtype, y_dtype, ctas)) {
+    pdm_net_tc_args t;
+    memset(&t, 0, sizeof(t));
+    t.x = static_cast<const uint8_t*>(dev_images);
+    t.y = static_cast<const uint8_t*>(dev_labels);
+    t.pool_rows = pool_samples;
+    t.batch = batch;
+    t.nsteps = nsteps;
+    t.params = e->params; t.m = e->m; t.v = e->v;
+    t.metrics = e->metrics;
+    t.hyper = *hyper;
+    if (e->comm != nullptr) {
+      int rc = pdm_comm_peers_block(e->comm, &t.peers, nsteps);
+      if (rc != PDM_OK) return rc;
+    }
+    PDM_CHECK_CUDA(cudaEventRecord(e->ev_begin, st));
+    int rc = pdm_net_tc_run(&t, st);
+    if (rc != PDM_OK) return rc;
+    PDM_CHECK_CUDA(cudaEventRecord(e->ev_end, st));
+    PDM_CHECK_CUDA(cudaStreamSynchronize(st));
+    e->last_launches = 1;
+    if (device_ms) {
+      float ms = 0.f;
+      PDM_CHECK_CUDA(cudaEventElapsedTime(&ms, e->ev_begin, e->ev_end));
+      *device_ms = ms;
+    }
+    return PDM_OK;
+  }
+  e->last_launches = nsteps;
   PDM_CHECK_CUDA(cudaEventRecord(e->ev_begin, st));
   for (int64_t i = 0; i < nsteps; ++i) {
     const int64_t b = i % nb;
@@ -682,6 +720,38 @@ int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, 
   cudaStream_t cs = e->stream[0];
   PDM_CHECK_CUDA(cudaEventRecord(e->ev_begin, cs));
   PDM_CHECK_CUDA(cudaMemcpyAsync(e->idx_dev, e->idx_host, (size_t)count * sizeof(int32_t), cudaMemcpyHostToDevice, cs));
+  if (use_tc(e, PDM_U8, PDM_U8, ctas)) {
+    // the whole pass is one launch: the kernel's producer warps gather every step's rows themselves
+    pdm_net_tc_args t;
+    memset(&t, 0, sizeof(t));
+    t.x = pl.images;
+    t.y = pl.labels;
+    t.row_index = e->idx_dev;
+    t.pool_rows = pl.n;
+    t.count = count;
+    t.batch = batch;
+    t.params = e->params; t.m = e->m; t.v = e->v;
+    t.metrics = e->metrics;
+    t.step_out = e->host_results_dev;
+    t.hyper = *hyper;
+    if (e->comm != nullptr) {
+      rc = pdm_comm_peers_block(e->comm, &t.peers, nsteps);
+      if (rc != PDM_OK) return rc;
+    }
+    rc = pdm_net_tc_run(&t, cs);
+    if (rc != PDM_OK) return rc;
+    e->last_launches = 1;
+    PDM_CHECK_CUDA(cudaEventRecord(e->ev_end, cs));
+    PDM_CHECK_CUDA(cudaStreamSynchronize(cs));
+    if (device_ms) {
+      float ms = 0.f;
+      PDM_CHECK_CUDA(cudaEventElapsedTime(&ms, e->ev_begin, e->ev_end));
+      *device_ms = ms;
+    }
+    if (step_results) memcpy(step_results, e->host_results, (size_t)nsteps * 2 * sizeof(float));
+    return PDM_OK;
+  }
+  e->last_launches = nsteps;
   for (int64_t b = 0; b < nsteps; ++b) {
     const int n = (int)std::min<int64_t>(batch, count - b * batch);
     pdm_net_step_args a;
@@ -734,6 +804,7 @@ int pdm_engine_metrics(pdm_engine* e, double out[4], int reset) {
   return PDM_OK;
 }
 
+int64_t pdm_engine_last_launches(pdm_engine* e) { return e ? e->last_launches : 0; }
 void* pdm_engine_scratch(pdm_engine* e) { return e ? e->scratch : nullptr; }
 void* pdm_engine_sync_words(pdm_engine* e) { return e ? e->sync : nullptr; }
 void* pdm_engine_metrics_ptr(pdm_engine* e) { return e ? e->metrics : nullptr; }

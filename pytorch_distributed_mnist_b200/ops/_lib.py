@@ -58,6 +58,15 @@ class NetStepArgs(ctypes.Structure):
                 ('inputs_stable', ctypes.c_int32)]
 
 
+class NetTcArgs(ctypes.Structure):
+    _fields_ = [('x', c_void_p), ('y', c_void_p), ('row_index', c_void_p),
+                ('pool_rows', ctypes.c_int64), ('first_batch', ctypes.c_int64), ('count', ctypes.c_int64),
+                ('batch', ctypes.c_int32), ('nsteps', ctypes.c_int64),
+                ('params', c_void_p), ('m', c_void_p), ('v', c_void_p),
+                ('grad_out', c_void_p), ('logits_out', c_void_p), ('metrics', c_void_p), ('step_out', c_void_p),
+                ('hyper', Hyper), ('peers', Peers)]
+
+
 class NativeError(RuntimeError):
     pass
 
@@ -71,6 +80,9 @@ def _declare(lib):
     lib.pdm_net_default_ctas.argtypes = [c_int]
     if hasattr(lib, 'pdm_net_train_step_static'):
         lib.pdm_net_train_step_static.argtypes = [ctypes.POINTER(NetStepArgs), c_void_p]
+    lib.pdm_net_tc_supported.argtypes = [c_int]
+    lib.pdm_net_tc_run.argtypes = [ctypes.POINTER(NetTcArgs), c_void_p]
+    lib.pdm_net_tc_trace_read.argtypes = [c_void_p]
     lib.pdm_net_eval_step.argtypes = [c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]
     lib.pdm_net_forward.argtypes = [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]
     lib.pdm_optim_step.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
@@ -103,6 +115,8 @@ def _declare(lib):
     lib.pdm_engine_run_device_typed.argtypes = [c_void_p, c_void_p, c_int, c_void_p, c_int, ctypes.c_int64, c_int,
                                                 ctypes.c_int64, ctypes.POINTER(Hyper), c_int, ctypes.POINTER(c_float)]
     lib.pdm_engine_metrics.argtypes = [c_void_p, ctypes.POINTER(ctypes.c_double), c_int]
+    lib.pdm_engine_last_launches.argtypes = [c_void_p]
+    lib.pdm_engine_last_launches.restype = ctypes.c_int64
     lib.pdm_engine_place_dataset.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_int64, c_int]
     lib.pdm_engine_run_gather.argtypes = [c_void_p, c_void_p, ctypes.c_int64, c_int, ctypes.POINTER(Hyper), c_int,
                                           c_void_p, ctypes.POINTER(c_float)]

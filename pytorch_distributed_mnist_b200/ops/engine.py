@@ -118,7 +118,7 @@ class NetEngine(object):
                                                 int(ctas), out.ctypes.data if out is not None else None,
                                                 ctypes.byref(ms)), 'pdm_engine_run(train)')
         self.optimizer.step_count += nsteps
-        self.launches += nsteps
+        self.launches += int(self._lib.pdm_engine_last_launches(self._h))
         if self.comm is not None and hasattr(self.comm, 'check_status'):
             self.comm.check_status()
         return out, float(ms.value)
@@ -146,7 +146,7 @@ class NetEngine(object):
             _lib.dtype_code(dev_labels), int(dev_labels.numel()), int(batch), int(nsteps), ctypes.byref(h), int(ctas),
             ctypes.byref(ms)), 'pdm_engine_run_device')
         self.optimizer.step_count += nsteps
-        self.launches += nsteps
+        self.launches += int(self._lib.pdm_engine_last_launches(self._h))
         if self.comm is not None and hasattr(self.comm, 'check_status'):
             self.comm.check_status()
         return float(ms.value)
