@@ -92,7 +92,7 @@ struct Misc {                     // lives at kOffMisc
   float wsum[2][16];              // per warp partial of sum_k W[n][k] over this CTA's columns
   float db[16];
   float adamc[2][4];              // by step parity: step_size, 1 / bc2_sqrt, first, unused
-  float lossw[2][2];              // per warp {loss, correct} of this CTA's rows of the current block
+  float lossw[3][2];              // per warp {loss, correct} of this CTA's rows of the current block
   float lossbuf[kCtas][2];        // CTA 0: per-CTA {loss sum, correct}
   uint8_t ys[kBlkRows];           // labels of the current block (written by the producers with the tile)
 };
@@ -118,6 +118,7 @@ struct TcArgs {
   float lr, beta1, beta2, eps, wd;
   long long step0;                // 1-based index of the first update
   float inv_world;
+  int dbg;                        // bring-up switches (PDM_TC_DBG bit mask); 0 in production
   long long* trace;               // optional [13][kTraceSteps][32] clock64 stamps per CTA (PDM_TC_TRACE=1)
   pdm_peers peers;
 };
@@ -152,6 +153,21 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "bra WAIT_%=;\n\t"
       "DONE_%=:\n\t"
       "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// The same wait for warps that are far ahead of the critical path (the producers): sleep between polls so
+// that their polling does not compete with the epilogue warps for issue slots and the shared-memory pipe.
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (true) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}" : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    if (done) break;
+    __nanosleep(128);
+  }
 }
 __device__ __forceinline__ uint32_t mapa(uint32_t local, uint32_t cta) {
   uint32_t r;
@@ -353,7 +369,10 @@ __device__ __forceinline__ void producer_loop(const TcArgs& a, uint8_t* smem, Mi
       // here it is off every critical path, the optimizer threads read it several barriers later
       if (pt == 0 && blk == 0) adam_consts(a, step, ms->adamc[step & 1]);
       TC_TRACE(pt == 32, step, 16);
-      if (it > 0) mbar_wait(&ms->bar_wg, (it - 1) & 1u);      // previous block's MMAs are done with the tile
+      if (it > 0) {                                            // previous block's MMAs are done with the tile
+        if (a.dbg & 1) mbar_wait(&ms->bar_wg, (it - 1) & 1u);
+        else mbar_wait_relaxed(&ms->bar_wg, (it - 1) & 1u);
+      }
       TC_TRACE(pt == 32, step, 17);
 #pragma unroll
       for (int j = 0; j < kItems; ++j) {
@@ -510,7 +529,6 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
   const bool is_bias = t == kCols;                       // thread 64 keeps a replica of the bias
   float* xbuf = reinterpret_cast<float*>(smem + kOffXbuf);
   float* stage = reinterpret_cast<float*>(smem + kOffStage);
-  float* zbuf = reinterpret_cast<float*>(smem + kOffZbuf);
   uint8_t* dlop = smem + kOffDlop;
   const uint32_t xbuf_s = smem_u32(xbuf), stage_s = smem_u32(stage), dlop_s = smem_u32(dlop);
   const uint32_t p1_s = smem_u32(&ms->bar_p1), p2_s = smem_u32(&ms->bar_p2), loss_s = smem_u32(&ms->bar_loss);
@@ -593,73 +611,67 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
       }
       mbar_wait(&ms->bar_xfull, par);          // (long complete) acquire the producers' label stores
 
-      // ---- 2. owner: sum the 13 partials (all threads), then one thread per row: soft-max, loss,
-      //         top-1, dlogits as three bf16 terms straight into the wgrad operand ----
+      // ---- 2. owner: two lanes per row (5 classes each): sum the 13 partials, soft-max, loss, top-1,
+      //         dlogits as three bf16 terms straight into the wgrad operand ----
       TC_TRACE(t == 0, step, 2);
       mbar_wait(&ms->bar_p1, par);
       TC_TRACE(t == 0, step, 3);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int i = t + kEpiThreads * j;
-        if (i < my_rows * kOut) {
-          const int c = i % kOut;
-          float z = ms->bias[c];
-#pragma unroll
-          for (int src = 0; src < kCtas; ++src) z += xbuf[src * kOwnRows * kOut + i];
-          zbuf[i] = z;
-        }
-      }
-      epi_sync();
       float my_loss = 0.f, my_hit = 0.f;
-      if (t < my_rows) {
-        const int r = cta * kOwnRows + t;
-        const bool valid = r < b.rows;
-        float z[kOut];
+      {
+        const int lr = t >> 1, half = t & 1;                 // lr < 64: rows beyond my_rows idle along (shuffles need every lane)
+        const bool active = lr < my_rows;
+        const int r = cta * kOwnRows + lr;
+        const bool valid = active && r < b.rows;
+        const int c0 = half * 5;
+        float z[5];
 #pragma unroll
-        for (int n = 0; n < kOut; n += 2) {
-          const float2 zz = *reinterpret_cast<const float2*>(zbuf + t * kOut + n);
-          z[n] = zz.x;
-          z[n + 1] = zz.y;
+        for (int k = 0; k < 5; ++k) z[k] = ms->bias[c0 + k];
+        if (active) {
+#pragma unroll
+          for (int src = 0; src < kCtas; ++src) {
+#pragma unroll
+            for (int k = 0; k < 5; ++k) z[k] += xbuf[(src * kOwnRows + lr) * kOut + c0 + k];
+          }
         }
-        const int y = (int)ms->ys[r];
-        float mx = z[0];
+        const int y = active ? (int)ms->ys[r] : 0;
+        float mx = fmaxf(fmaxf(fmaxf(z[0], z[1]), fmaxf(z[2], z[3])), z[4]);
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        float e[5], s = 0.f, zy = -INFINITY;
 #pragma unroll
-        for (int n = 1; n < kOut; ++n) mx = fmaxf(mx, z[n]);
-        float e[kOut], s = 0.f, zy = z[0];
-        bool hit = true;
-#pragma unroll
-        for (int n = 0; n < kOut; ++n) {
-          e[n] = __expf(z[n] - mx);                          // ex2.approx: <= 2e-6 relative on the probabilities
-          s += e[n];
-          zy = n == y ? z[n] : zy;
+        for (int k = 0; k < 5; ++k) {
+          e[k] = __expf(z[k] - mx);                          // ex2.approx: <= 2e-6 relative on the probabilities
+          s += e[k];
+          zy = (c0 + k) == y ? z[k] : zy;
         }
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        zy = fmaxf(zy, __shfl_xor_sync(0xffffffffu, zy, 1));
+        bool beaten = false;
 #pragma unroll
-        for (int n = 0; n < kOut; ++n) hit = hit && !(z[n] > zy || (z[n] == zy && n < y));
+        for (int k = 0; k < 5; ++k) beaten = beaten || z[k] > zy || (z[k] == zy && (c0 + k) < y);
+        const int other_beaten = __shfl_xor_sync(0xffffffffu, beaten ? 1 : 0, 1);   // every lane shuffles (no short-circuit)
+        beaten = beaten || other_beaten != 0;
         const float inv_s = __fdividef(1.0f, s);
-        uint32_t hi[kOut], mid[kOut], lo[kOut];
+        if (active) {
+          // wgrad B operand, MN-major 8x8 core matrices: [split][n / 8][row][n % 8] bf16 (columns 10-15 stay zero)
 #pragma unroll
-        for (int n = 0; n < kOut; ++n) {
-          const float d = valid ? (e[n] * inv_s - (n == y ? 1.f : 0.f)) * inv_batch : 0.f;
-          split3(d, hi[n], mid[n], lo[n]);
-          if (a.logits_out != nullptr && last_step && valid) a.logits_out[(size_t)(blk * kBlkRows + r) * kOut + n] = z[n];
+          for (int k = 0; k < 5; ++k) {
+            const int n = c0 + k;
+            const float d = valid ? (e[k] * inv_s - (n == y ? 1.f : 0.f)) * inv_batch : 0.f;
+            uint32_t hi, mid, lo;
+            split3(d, hi, mid, lo);
+            uint8_t* dst = dlop + (uint32_t)(n >> 3) * 8192u + (uint32_t)r * 16u + (uint32_t)(n & 7) * 2u;
+            *reinterpret_cast<uint16_t*>(dst) = (uint16_t)hi;
+            *reinterpret_cast<uint16_t*>(dst + kDlSplitBytes) = (uint16_t)mid;
+            *reinterpret_cast<uint16_t*>(dst + 2 * kDlSplitBytes) = (uint16_t)lo;
+            if (a.logits_out != nullptr && last_step && valid) a.logits_out[(size_t)(blk * kBlkRows + r) * kOut + n] = z[k];
+          }
         }
-        // wgrad B operand, MN-major 8x8 core matrices: [split][n / 8][row][n % 8] bf16
-        const uint32_t off = (uint32_t)r * 16u;
-        *reinterpret_cast<uint4*>(dlop + off) =
-            make_uint4(hi[0] | (hi[1] << 16), hi[2] | (hi[3] << 16), hi[4] | (hi[5] << 16), hi[6] | (hi[7] << 16));
-        *reinterpret_cast<uint4*>(dlop + 8192u + off) = make_uint4(hi[8] | (hi[9] << 16), 0u, 0u, 0u);
-        *reinterpret_cast<uint4*>(dlop + kDlSplitBytes + off) =
-            make_uint4(mid[0] | (mid[1] << 16), mid[2] | (mid[3] << 16), mid[4] | (mid[5] << 16), mid[6] | (mid[7] << 16));
-        *reinterpret_cast<uint4*>(dlop + kDlSplitBytes + 8192u + off) = make_uint4(mid[8] | (mid[9] << 16), 0u, 0u, 0u);
-        *reinterpret_cast<uint4*>(dlop + 2 * kDlSplitBytes + off) =
-            make_uint4(lo[0] | (lo[1] << 16), lo[2] | (lo[3] << 16), lo[4] | (lo[5] << 16), lo[6] | (lo[7] << 16));
-        *reinterpret_cast<uint4*>(dlop + 2 * kDlSplitBytes + 8192u + off) = make_uint4(lo[8] | (lo[9] << 16), 0u, 0u, 0u);
-        if (valid) {
+        if (valid && half == 0) {
           my_loss = (mx + logf(s)) - zy;
-          my_hit = hit ? 1.f : 0.f;
+          my_hit = beaten ? 0.f : 1.f;
         }
       }
-      if (warp < 2) {                                        // rows 0-31 and 32-39: fixed butterfly, deterministic
+      if (warp < 3) {                                        // rows 0-15, 16-31, 32-39: fixed butterfly, deterministic
 #pragma unroll
         for (int o = 16; o >= 1; o >>= 1) {
           my_loss += __shfl_xor_sync(0xffffffffu, my_loss, o);
@@ -678,8 +690,8 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
         bulk_s2s(mapa(dlop_s + off, dest), dlop_s + off, (uint32_t)my_rows * 16u, mapa(p2_s, dest));
       }
       if (t == 0)
-        st_async2(mapa(smem_u32(&ms->lossbuf[cta][0]), 0u), ms->lossw[0][0] + ms->lossw[1][0], ms->lossw[0][1] + ms->lossw[1][1],
-                  mapa(loss_s, 0u));
+        st_async2(mapa(smem_u32(&ms->lossbuf[cta][0]), 0u), (ms->lossw[0][0] + ms->lossw[1][0]) + ms->lossw[2][0],
+                  (ms->lossw[0][1] + ms->lossw[1][1]) + ms->lossw[2][1], mapa(loss_s, 0u));
       tc_fence_before();
       mbar_arrive(&ms->bar_dl);                              // own rows written, forward accumulator drained
       TC_TRACE(t == 0, step, 4);
@@ -946,6 +958,7 @@ extern "C" int pdm_net_tc_run(const pdm_net_tc_args* g, pdm_stream_t stream) {
   a.lr = h.lr; a.beta1 = h.beta1; a.beta2 = h.beta2; a.eps = h.eps; a.wd = h.weight_decay;
   a.step0 = h.step;
   a.inv_world = world > 1 ? 1.0f / (float)world : 1.0f;
+  { const char* e = getenv("PDM_TC_DBG"); a.dbg = e && *e ? atoi(e) : 0; }
   a.trace = tc_trace_buffer();
   a.peers = g->peers;
   a.peers.world = world;
