@@ -193,6 +193,7 @@ int pdm_net_train_step_static(const pdm_net_step_args* args, pdm_stream_t stream
  * (hi + mid + lo), so products are exact and accumulation is fp32 -- fp32-faithful, not bf16.
  * Softmax uses ex2.approx, the Adam update sqrt.approx / div.approx (<= 2 ulp each). */
 #define PDM_TC_CLUSTER 13
+#define PDM_TC_MAX_LAUNCH_STEPS 8192   /* longer runs are cut into launches of at most this many steps */
 typedef struct pdm_net_tc_args {
   const uint8_t* x;
   const uint8_t* y;

@@ -214,8 +214,10 @@ void worker_main(pdm_engine* e) {
 
 // The persistent tensor-core kernel (net_tc.cu) takes a whole pass in one launch: used for raw uint8
 // inputs whenever the device can launch it and the caller did not ask for a specific CTA count.
-bool use_tc(const pdm_engine* e, int x_dtype, int y_dtype, int ctas) {
-  return x_dtype == PDM_U8 && y_dtype == PDM_U8 && ctas == 0 && pdm_net_tc_supported(e->device) == 1;
+// It runs on one 13-SM cluster, so beyond ~1024 rows per step the 148-SM per-step kernel is faster
+// (measured: 8.3 vs 9.6 us at batch 512, 57 vs 27 us at batch 4096; benchmarks/tc_sweep.py).
+bool use_tc(const pdm_engine* e, int x_dtype, int y_dtype, int ctas, int batch) {
+  return x_dtype == PDM_U8 && y_dtype == PDM_U8 && ctas == 0 && batch <= 1024 && pdm_net_tc_supported(e->device) == 1;
 }
 
 int ensure_results(pdm_engine* e, int64_t nsteps) {
@@ -512,7 +514,7 @@ int pdm_engine_run_device_typed(pdm_engine* e, const void* dev_images, int x_dty
   PDM_CHECK_CUDA(cudaSetDevice(e->device));
   const int64_t nb = pool_samples / batch;
   cudaStream_t st = e->stream[0];
-  if (nsteps >= 1 && use_tc(e, x_dtype, y_dtype, ctas)) {
+  if (nsteps >= 1 && use_tc(e, x_dtype, y_dtype, ctas, batch)) {
     pdm_net_tc_args t;
     memset(&t, 0, sizeof(t));
     t.x = static_cast<const uint8_t*>(dev_images);
@@ -532,7 +534,7 @@ int pdm_engine_run_device_typed(pdm_engine* e, const void* dev_images, int x_dty
     if (rc != PDM_OK) return rc;
     PDM_CHECK_CUDA(cudaEventRecord(e->ev_end, st));
     PDM_CHECK_CUDA(cudaStreamSynchronize(st));
-    e->last_launches = 1;
+    e->last_launches = (nsteps + PDM_TC_MAX_LAUNCH_STEPS - 1) / PDM_TC_MAX_LAUNCH_STEPS;
     if (device_ms) {
       float ms = 0.f;
       PDM_CHECK_CUDA(cudaEventElapsedTime(&ms, e->ev_begin, e->ev_end));
@@ -720,7 +722,7 @@ int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, 
   cudaStream_t cs = e->stream[0];
   PDM_CHECK_CUDA(cudaEventRecord(e->ev_begin, cs));
   PDM_CHECK_CUDA(cudaMemcpyAsync(e->idx_dev, e->idx_host, (size_t)count * sizeof(int32_t), cudaMemcpyHostToDevice, cs));
-  if (use_tc(e, PDM_U8, PDM_U8, ctas)) {
+  if (use_tc(e, PDM_U8, PDM_U8, ctas, batch)) {
     // the whole pass is one launch: the kernel's producer warps gather every step's rows themselves
     pdm_net_tc_args t;
     memset(&t, 0, sizeof(t));
@@ -740,7 +742,7 @@ int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, 
     }
     rc = pdm_net_tc_run(&t, cs);
     if (rc != PDM_OK) return rc;
-    e->last_launches = 1;
+    e->last_launches = (nsteps + PDM_TC_MAX_LAUNCH_STEPS - 1) / PDM_TC_MAX_LAUNCH_STEPS;
     PDM_CHECK_CUDA(cudaEventRecord(e->ev_end, cs));
     PDM_CHECK_CUDA(cudaStreamSynchronize(cs));
     if (device_ms) {

@@ -34,6 +34,7 @@
 //     summed in rank order (bit-identical replicas), inside the same kernel.
 #include "common.cuh"
 
+#include <cuda_bf16.h>
 #include <math.h>
 #include <stdlib.h>
 
@@ -91,7 +92,6 @@ struct Misc {                     // lives at kOffMisc
   float bias[16];
   float wsum[2][16];              // per warp partial of sum_k W[n][k] over this CTA's columns
   float db[16];
-  float adamc[2][4];              // by step parity: step_size, 1 / bc2_sqrt, first, unused
   float lossw[3][2];              // per warp {loss, correct} of this CTA's rows of the current block
   float lossbuf[kCtas][2];        // CTA 0: per-CTA {loss sum, correct}
   uint8_t ys[kBlkRows];           // labels of the current block (written by the producers with the tile)
@@ -117,6 +117,7 @@ struct TcArgs {
   int opt;
   float lr, beta1, beta2, eps, wd;
   long long step0;                // 1-based index of the first update
+  const float2* adam;             // per step of this launch: {lr / (1 - beta1^t), 1 / sqrt(1 - beta2^t)} (host-computed, double precision)
   float inv_world;
   int dbg;                        // bring-up switches (PDM_TC_DBG bit mask); 0 in production
   long long* trace;               // optional [13][kTraceSteps][32] clock64 stamps per CTA (PDM_TC_TRACE=1)
@@ -236,9 +237,8 @@ constexpr uint32_t kIdescBase = (1u << 4) | (1u << 7) | (1u << 10) | ((48u >> 3)
 constexpr uint32_t kIdescFwd = kIdescBase;                              // both operands K-major
 constexpr uint32_t kIdescWg = kIdescBase | (1u << 15) | (1u << 16);     // both operands MN-major
 
-__device__ __forceinline__ uint32_t bf16_bits(float f) {                // round-to-nearest-even
-  uint32_t u = __float_as_uint(f);
-  return (u + 0x7FFFu + ((u >> 16) & 1u)) >> 16;
+__device__ __forceinline__ uint32_t bf16_bits(float f) {                // round-to-nearest-even, one cvt instruction
+  return (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(f));
 }
 __device__ __forceinline__ float bf16_val(uint32_t b) { return __uint_as_float(b << 16); }
 // f = hi + mid + lo with three bf16 terms (24 mantissa bits: exact for every fp32 in range)
@@ -296,10 +296,19 @@ __device__ __forceinline__ Blk make_blk(int n_step, int blk) {
   b.last = left <= kBlkRows;
   return b;
 }
-// dataset row of local row r of (step, blk)
-__device__ __forceinline__ long long row_id(const TcArgs& a, long long step, int blk, int r) {
-  if (a.row_index != nullptr) return (long long)__ldg(a.row_index + step * (long long)a.batch + blk * kBlkRows + r);
-  return ((a.first_batch + step) % a.pool_batches) * (long long)a.batch + blk * kBlkRows + r;
+// dataset rows of a block: pool mode = base + r, plan mode = index[r] (one 64-bit modulo per block, not per row)
+struct Rows {
+  const int32_t* index;
+  long long base;
+  __device__ __forceinline__ long long operator()(int r) const { return index != nullptr ? (long long)__ldg(index + r) : base + r; }
+};
+__device__ __forceinline__ Rows block_rows(const TcArgs& a, long long step, int blk) {
+  Rows q;
+  q.index = nullptr;
+  q.base = 0;
+  if (a.row_index != nullptr) q.index = a.row_index + step * (long long)a.batch + blk * kBlkRows;
+  else q.base = ((a.first_batch + step) % a.pool_batches) * (long long)a.batch + blk * kBlkRows;
+  return q;
 }
 
 __device__ __forceinline__ uint4 ld_stream16(const uint8_t* p) {
@@ -320,20 +329,6 @@ __device__ __forceinline__ void px4_to_bf16(uint32_t w, uint32_t& lo, uint32_t& 
   hi = __byte_perm(__float_as_uint(f2), __float_as_uint(f3), 0x7632);
 }
 
-// Adam bias corrections of one step (same arithmetic as net_step.cu's host side, in double).
-__device__ __noinline__ void adam_consts(const TcArgs& a, long long step, float* out) {
-  const long long idx = a.step0 + step;
-  const double sidx = (double)(idx < 1 ? 1 : idx);
-  float step_size = 0.f, inv_bc2 = 1.f;
-  if (a.opt == PDM_OPT_ADAM) {
-    step_size = (float)((double)a.lr / (1.0 - pow((double)a.beta1, sidx)));
-    inv_bc2 = (float)(1.0 / sqrt(1.0 - pow((double)a.beta2, sidx)));
-  }
-  out[0] = step_size;
-  out[1] = inv_bc2;
-  out[2] = idx <= 1 ? 1.f : 0.f;
-}
-
 // ---------------------------------------------------------------------------- producer warps
 // 224 threads stream the rows (and labels) of the next block into registers while the current block
 // computes, then (once the wgrad MMAs of the current block have finished reading the tile) convert
@@ -348,6 +343,7 @@ __device__ __forceinline__ void producer_loop(const TcArgs& a, uint8_t* smem, Mi
     const int nblk = (n_step + kBlkRows - 1) / kBlkRows;
     for (int blk = 0; blk < nblk; ++blk, ++it) {
       const Blk b = make_blk(n_step, blk);
+      const Rows rows = block_rows(a, step, blk);
       constexpr int kItems = (kBlkRows * 4 + kProdThreads - 1) / kProdThreads;   // 10
       uint4 raw[kItems];
 #pragma unroll
@@ -356,18 +352,15 @@ __device__ __forceinline__ void producer_loop(const TcArgs& a, uint8_t* smem, Mi
         const int r = item >> 2, q = item & 3;
         raw[j] = make_uint4(0u, 0u, 0u, 0u);
         if (r < b.rows && q * 16 < valid_cols)
-          raw[j] = ld_stream16(a.x + row_id(a, step, blk, r) * kIn + col0 + q * 16);
+          raw[j] = ld_stream16(a.x + rows(r) * kIn + col0 + q * 16);
       }
       uint32_t lab[3];                                         // labels travel with the tile (three rows per thread)
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
         const int r = pt + kProdThreads * j;
         lab[j] = 0u;
-        if (r < b.rows) lab[j] = min((uint32_t)__ldg(a.y + row_id(a, step, blk, r)), (uint32_t)(kOut - 1));
+        if (r < b.rows) lab[j] = min((uint32_t)__ldg(a.y + rows(r)), (uint32_t)(kOut - 1));
       }
-      // one producer thread also prepares the step's Adam bias corrections (two double-precision pow):
-      // here it is off every critical path, the optimizer threads read it several barriers later
-      if (pt == 0 && blk == 0) adam_consts(a, step, ms->adamc[step & 1]);
       TC_TRACE(pt == 32, step, 16);
       if (it > 0) {                                            // previous block's MMAs are done with the tile
         if (a.dbg & 1) mbar_wait(&ms->bar_wg, (it - 1) & 1u);
@@ -507,18 +500,24 @@ __device__ __forceinline__ void publish_weights(uint8_t* smem, Misc* ms, int t, 
     *reinterpret_cast<uint16_t*>(wop + 2 * kWopSplitBytes + off) = (uint16_t)lo;
     s[n] = p[n];
   }
-  // ten independent butterfly reductions, level by level (the shuffles of one level overlap)
+  // Transposing warp reduction: 16 shuffles for the ten sums instead of 50.  After the four halving
+  // levels lane L holds value ((L >> 1) & 15) summed over 16 lanes; one more exchange completes it.
+  float r[16];
 #pragma unroll
-  for (int o = 16; o >= 1; o >>= 1) {
+  for (int n = 0; n < 16; ++n) r[n] = n < kOut ? s[n] : 0.f;
 #pragma unroll
-    for (int n = 0; n < kOut; ++n) s[n] += __shfl_xor_sync(0xffffffffu, s[n], o);
+  for (int off = 16, h = 8; off >= 2; off >>= 1, h >>= 1) {
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < h; ++i) {
+      const float keep = upper ? r[i + h] : r[i];
+      const float send = upper ? r[i] : r[i + h];
+      r[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
   }
-  if (lane < kOut) {
-    float mine = s[0];
-#pragma unroll
-    for (int n = 1; n < kOut; ++n) mine = lane == n ? s[n] : mine;
-    ms->wsum[warp][lane] = mine;
-  }
+  r[0] += __shfl_xor_sync(0xffffffffu, r[0], 1);
+  const int which = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+  if ((lane & 1) == 0 && which < kOut) ms->wsum[warp][which] = r[0];
 }
 
 // ---------------------------------------------------------------------------- epilogue / optimizer warps
@@ -547,14 +546,6 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
       if (a.v != nullptr) v[n] = a.v[idx];
     }
   }
-  if (t < kCols) publish_weights(smem, ms, t, lane, warp, p);
-  if (is_bias) {
-#pragma unroll
-    for (int n = 0; n < kOut; ++n) ms->bias[n] = p[n];
-  }
-  fence_async_smem();
-  mbar_arrive(&ms->bar_wop);                               // phase 0: the first step's weights
-  epi_sync();
 
   float step_loss = 0.f, step_correct = 0.f;               // CTA 0, thread 0
   uint32_t it = 0;
@@ -563,6 +554,18 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
     const int nblk = (n_step + kBlkRows - 1) / kBlkRows;
     const float inv_batch = 1.0f / (float)n_step;
     const bool last_step = step + 1 == a.nsteps;
+    // ---- 0. this step's weights -> the forward B operand (three bf16 terms) ----
+    if (t < kCols) publish_weights(smem, ms, t, lane, warp, p);
+    if (is_bias) {
+#pragma unroll
+      for (int n = 0; n < kOut; ++n) ms->bias[n] = p[n];
+    }
+    fence_async_smem();
+    tc_fence_before();
+    mbar_arrive(&ms->bar_wop);
+    epi_sync();
+    TC_TRACE(t == 0, step, 13);
+    const float2 adam_c = __ldg(a.adam + step);           // consumed at the end of the step: the latency is hidden
     float wsumn[kOut];
 #pragma unroll
     for (int n = 0; n < kOut; ++n) wsumn[n] = kShift * (ms->wsum[0][n] + ms->wsum[1][n]);
@@ -743,9 +746,8 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
           g[n] = is_bias ? dbn : (owns_col ? fmaf(kScale, gsum[n], -kShift * dbn) : 0.f);
         }
         if (a.peers.world > 1) ll_exchange(a, a.peers.seq + (uint32_t)step, cta, t, g);
-        const float* ac = ms->adamc[step & 1];
-        const float step_size = ac[0], inv_bc2 = ac[1];
-        const bool first = ac[2] != 0.f;
+        const float step_size = adam_c.x, inv_bc2 = adam_c.y;
+        const bool first = a.step0 + step <= 1;
         if (owns_col || is_bias) {
 #pragma unroll
           for (int n = 0; n < kOut; ++n) {
@@ -765,19 +767,8 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
             }
           }
         }
-        TC_TRACE(t == 0, step, 22);
-        if (t < kCols) publish_weights(smem, ms, t, lane, warp, p);
-        if (is_bias) {
-#pragma unroll
-          for (int n = 0; n < kOut; ++n) ms->bias[n] = p[n];
-        }
       }
-      TC_TRACE(t == 0, step, 23);
-      fence_async_smem();
-      tc_fence_before();
-      mbar_arrive(&ms->bar_wop);
-      epi_sync();
-      TC_TRACE(t == 0, step, 13);
+      TC_TRACE(t == 0, step, 22);
     }
   }
 }
@@ -904,6 +895,27 @@ extern "C" int pdm_net_tc_trace_read(long long* out) {
   return PDM_OK;
 }
 
+// Adam's per-step bias corrections are computed here, on the host, in double precision (the same arithmetic as
+// torch.optim.Adam and net_step.cu) and handed to the kernel through a fixed device array: no pow() in the
+// kernel's instruction stream.  A launch covers at most kMaxLaunchSteps steps; longer runs are cut into launches.
+// The array is shared by all calls on a device: they must be ordered on one stream (the engine's are).
+constexpr long long kMaxLaunchSteps = PDM_TC_MAX_LAUNCH_STEPS;
+static __device__ float2 g_adam_consts[kMaxLaunchSteps];
+
+static int adam_array(float2** out) {
+  static float2* addr[64];
+  int dev = -1;
+  PDM_CHECK_CUDA(cudaGetDevice(&dev));
+  PDM_REQUIRE(dev >= 0 && dev < 64, PDM_ERR_LIMIT, "pdm_net_tc_run: device ordinal %d outside [0, 64)", dev);
+  if (addr[dev] == nullptr) {
+    void* p = nullptr;
+    PDM_CHECK_CUDA(cudaGetSymbolAddress(&p, g_adam_consts));
+    addr[dev] = static_cast<float2*>(p);
+  }
+  *out = addr[dev];
+  return PDM_OK;
+}
+
 extern "C" int pdm_net_tc_run(const pdm_net_tc_args* g, pdm_stream_t stream) {
   PDM_REQUIRE(g != nullptr, PDM_ERR_ARG, "pdm_net_tc_run: args is NULL");
   PDM_REQUIRE(g->x && g->y && g->params, PDM_ERR_ARG, "pdm_net_tc_run: x, y and params are required");
@@ -915,18 +927,15 @@ extern "C" int pdm_net_tc_run(const pdm_net_tc_args* g, pdm_stream_t stream) {
               "pdm_net_tc_run: unknown optimizer %d", h.opt);
   PDM_REQUIRE(h.opt != PDM_OPT_ADAM || (g->m && g->v), PDM_ERR_ARG, "pdm_net_tc_run: Adam needs m and v");
   PDM_REQUIRE(!(h.opt == PDM_OPT_SGD && h.beta1 != 0.f) || g->m, PDM_ERR_ARG, "pdm_net_tc_run: SGD with momentum needs m");
-  TcArgs a;
-  memset(&a, 0, sizeof(a));
   long long nsteps = g->nsteps;
+  long long pool_batches = 0;
   if (g->row_index != nullptr) {
     PDM_REQUIRE(g->count >= 0, PDM_ERR_ARG, "pdm_net_tc_run: count must be >= 0");
     const long long need = (g->count + g->batch - 1) / g->batch;
     if (nsteps == 0 || nsteps > need) nsteps = need;
-    a.count = g->count;
   } else {
     PDM_REQUIRE(g->pool_rows >= g->batch, PDM_ERR_ARG, "pdm_net_tc_run: the pool holds fewer rows than one batch");
-    a.pool_batches = g->pool_rows / g->batch;
-    a.first_batch = g->first_batch % a.pool_batches;
+    pool_batches = g->pool_rows / g->batch;
   }
   if (nsteps == 0) return PDM_OK;
   const int world = g->peers.world > 1 ? g->peers.world : 1;
@@ -942,31 +951,58 @@ extern "C" int pdm_net_tc_run(const pdm_net_tc_args* g, pdm_stream_t stream) {
   PDM_REQUIRE(pdm_net_tc_supported(dev) == 1, PDM_ERR_STATE,
               "pdm_net_tc_run: device %d cannot launch a %d-CTA cluster with %u bytes of shared memory per CTA "
               "(or PDM_NET_TC=0)", dev, kCtas, kSmemBytes);
-  a.x = g->x;
-  a.y = g->y;
-  a.row_index = g->row_index;
-  a.batch = g->batch;
-  a.nsteps = nsteps;
-  a.params = g->params;
-  a.m = g->m;
-  a.v = g->v;
-  a.grad_out = g->grad_out;
-  a.logits_out = g->logits_out;
-  a.metrics = g->metrics;
-  a.step_out = g->step_out;
-  a.opt = h.opt;
-  a.lr = h.lr; a.beta1 = h.beta1; a.beta2 = h.beta2; a.eps = h.eps; a.wd = h.weight_decay;
-  a.step0 = h.step;
-  a.inv_world = world > 1 ? 1.0f / (float)world : 1.0f;
-  { const char* e = getenv("PDM_TC_DBG"); a.dbg = e && *e ? atoi(e) : 0; }
-  a.trace = tc_trace_buffer();
-  a.peers = g->peers;
-  a.peers.world = world;
+  float2* adam_dev = nullptr;
+  int rc = adam_array(&adam_dev);
+  if (rc != PDM_OK) return rc;
 
-  cudaLaunchConfig_t cfg;
-  cudaLaunchAttribute attr[1];
-  tc_launch_config(&cfg, attr, (cudaStream_t)stream);
-  void* params[] = {&a};
-  PDM_CHECK_CUDA(cudaLaunchKernelExC(&cfg, (const void*)net_tc_kernel, params));
+  static thread_local float2 adam_host[kMaxLaunchSteps];
+  for (long long done = 0; done < nsteps; done += kMaxLaunchSteps) {
+    const long long n = nsteps - done < kMaxLaunchSteps ? nsteps - done : kMaxLaunchSteps;
+    TcArgs a;
+    memset(&a, 0, sizeof(a));
+    a.x = g->x;
+    a.y = g->y;
+    a.batch = g->batch;
+    a.nsteps = n;
+    if (g->row_index != nullptr) {
+      a.row_index = g->row_index + done * g->batch;
+      a.count = g->count - done * g->batch;
+    } else {
+      a.pool_batches = pool_batches;
+      a.first_batch = (g->first_batch + done) % pool_batches;
+    }
+    a.params = g->params;
+    a.m = g->m;
+    a.v = g->v;
+    a.grad_out = g->grad_out;
+    a.logits_out = g->logits_out;
+    a.metrics = g->metrics;
+    a.step_out = g->step_out != nullptr ? g->step_out + 2 * done : nullptr;
+    a.opt = h.opt;
+    a.lr = h.lr; a.beta1 = h.beta1; a.beta2 = h.beta2; a.eps = h.eps; a.wd = h.weight_decay;
+    a.step0 = h.step + done;
+    a.inv_world = world > 1 ? 1.0f / (float)world : 1.0f;
+    a.adam = adam_dev;
+    a.trace = tc_trace_buffer();
+    a.peers = g->peers;
+    a.peers.world = world;
+    a.peers.seq = g->peers.seq + (uint32_t)done;
+    for (long long i = 0; i < n; ++i) {
+      const long long idx = a.step0 + i;
+      const double sidx = (double)(idx < 1 ? 1 : idx);
+      adam_host[i] = make_float2(0.f, 1.f);
+      if (h.opt == PDM_OPT_ADAM) {
+        adam_host[i].x = (float)((double)h.lr / (1.0 - pow((double)h.beta1, sidx)));
+        adam_host[i].y = (float)(1.0 / sqrt(1.0 - pow((double)h.beta2, sidx)));
+      }
+    }
+    // pageable source: the runtime stages it before returning, so adam_host may be reused at once
+    PDM_CHECK_CUDA(cudaMemcpyAsync(adam_dev, adam_host, (size_t)n * sizeof(float2), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    tc_launch_config(&cfg, attr, (cudaStream_t)stream);
+    void* params[] = {&a};
+    PDM_CHECK_CUDA(cudaLaunchKernelExC(&cfg, (const void*)net_tc_kernel, params));
+  }
   return PDM_OK;
 }
