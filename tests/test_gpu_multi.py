@@ -153,6 +153,67 @@ def _assert_close_after_adam(a, b, lr, steps):
     assert outliers <= d.numel() // 200, '{} of {} elements drifted'.format(outliers, d.numel())
 
 
+def _tc_worker(rank, world, port):
+    """The persistent tensor-core kernel across GPUs: one launch per rank runs 24 steps with the LL
+    exchange inside; oracle = stock DDP + torch.optim.Adam on the same per-rank batches."""
+    import torch.nn.functional as F
+    from pytorch_distributed_mnist_b200 import Net, FusedAdam, DistributedDataParallel
+    from pytorch_distributed_mnist_b200.ops import net_tc
+    from pytorch_distributed_mnist_b200.ops.engine import NetEngine
+    _init(rank, world, port)
+    try:
+        dev = torch.device('cuda', rank)
+        if not net_tc.supported(dev):
+            return
+        torch.manual_seed(70 + rank)
+        model = DistributedDataParallel(Net().to(dev), device_ids=[rank])
+        assert model.uses_peer
+        opt = FusedAdam(model.parameters(), lr=1e-3)
+        eng = NetEngine(opt.flat, opt, comm=model.comm, device=dev, max_batch=256, slots=4, workers=2)
+        ref = torch.nn.Linear(784, 10).to(dev)
+        ref.load_state_dict(model.module.fc.state_dict())
+        ref = torch.nn.parallel.DistributedDataParallel(ref, device_ids=[rank])
+        ropt = torch.optim.Adam(ref.parameters(), lr=1e-3)
+        B, nb, steps = 256, 6, 24
+        g = torch.Generator().manual_seed(500 + rank)
+        x = torch.randint(0, 256, (nb * B, 784), generator=g, dtype=torch.uint8)
+        x[torch.rand(nb * B, 784, generator=g) < 0.6] = 0
+        y = torch.randint(0, 10, (nb * B,), generator=g, dtype=torch.uint8)
+        xd, yd = x.to(dev), y.to(dev)
+        before = eng.launches
+        eng.train_device(xd, yd, B, steps)                  # ONE launch: 24 steps, all-reduce inside
+        assert eng.launches - before == 1
+        for i in range(steps):
+            s = (i % nb) * B
+            loss = F.cross_entropy(ref(xd[s:s + B].float().div(255).sub(MEAN).div(STD)), yd[s:s + B].long())
+            ropt.zero_grad()
+            loss.backward()
+            ropt.step()
+        torch.cuda.synchronize()
+        torch.testing.assert_close(model.module.fc.weight.detach(), ref.module.weight.detach(), rtol=1e-3, atol=2e-4)
+        torch.testing.assert_close(model.module.fc.bias.detach(), ref.module.bias.detach(), rtol=1e-3, atol=2e-4)
+        # a gather pass from pinned host memory continues the same run (sequence numbers carry on)
+        eng.set_dataset(x, y)
+        eng.place_dataset('zerocopy')
+        idx = torch.randperm(nb * B, generator=torch.Generator().manual_seed(3 + rank))[:1000]
+        st, _ = eng.train(idx, B)
+        assert st.shape == (4, 2) and opt.step_count == steps + 4
+        mine = opt.flat.params.clone()
+        others = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(others, mine)
+        for o in others:
+            assert torch.equal(o, mine), 'replicas diverged in the persistent tensor-core kernel'
+        model.comm.check_status()
+        eng.close()
+        model.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_persistent_tc_kernel_ll_allreduce(free_port):
+    mp.spawn(_tc_worker, args=(_world(), free_port), nprocs=_world())
+
+
 def _cnn_worker(rank, world, port, native=False):
     import pytorch_distributed_mnist_b200 as pdm
     _init(rank, world, port)
