@@ -262,8 +262,10 @@ def run_ours(opts):
                 'input_path': {
                     'staged': 'loader threads gather each shuffled batch into a pinned slot; one cudaMemcpyAsync H2D '
                               '(B*785 bytes) per step',
-                    'zerocopy': 'the step kernel loads its shuffled rows (B*785 bytes) every step straight from the '
-                                'page-locked (cudaHostRegister) host dataset over PCIe; index plan uploaded as B*4 bytes/step',
+                    'zerocopy': 'every step the kernel reads its shuffled rows (B*785 bytes) over PCIe straight from the '
+                                'page-locked (cudaHostRegister) host dataset: a feeder cluster of the persistent kernel gathers '
+                                'whole rows into a device ring one to four blocks ahead of the training cluster; index plan '
+                                'uploaded as B*4 bytes/step',
                 }.get(trainer.data_placement, trainer.data_placement),
                 'result_path': 'kernel stores {loss, correct} (8 bytes) into mapped pinned host memory every step',
                 'host_cores_per_rank': (os.cpu_count() or 0) // max(1, world),

@@ -193,6 +193,13 @@ int pdm_net_train_step_static(const pdm_net_step_args* args, pdm_stream_t stream
  * (hi + mid + lo), so products are exact and accumulation is fp32 -- fp32-faithful, not bf16.
  * Softmax uses ex2.approx, the Adam update sqrt.approx / div.approx (<= 2 ulp each). */
 #define PDM_TC_CLUSTER 13
+/* Optional feeder ring (plan mode): device scratch of PDM_TC_RING_BYTES.  With it the launch carries a
+ * second cluster that copies WHOLE rows of the coming blocks (784 contiguous bytes each: full-size PCIe
+ * reads when x / y are pinned host memory) into the ring, and the training cluster reads its 64-byte
+ * column slices from there through L2 instead of issuing 64-byte reads over PCIe. */
+#define PDM_TC_RING_SLOTS 4
+#define PDM_TC_RING_SLOT_BYTES (512 * 784 + 512)
+#define PDM_TC_RING_BYTES ((size_t)PDM_TC_RING_SLOTS * PDM_TC_RING_SLOT_BYTES + 256)
 #define PDM_TC_MAX_LAUNCH_STEPS 8192   /* longer runs are cut into launches of at most this many steps */
 typedef struct pdm_net_tc_args {
   const uint8_t* x;
@@ -210,6 +217,8 @@ typedef struct pdm_net_tc_args {
   float* step_out;
   pdm_hyper hyper;
   pdm_peers peers;
+  void* ring;            /* optional feeder ring, see PDM_TC_RING_BYTES (NULL: every CTA reads its slices directly) */
+  size_t ring_bytes;
 } pdm_net_tc_args;
 /* 1 when `device` can launch the cluster kernel (compute capability 10.x, 13-CTA clusters). */
 int pdm_net_tc_supported(int device);

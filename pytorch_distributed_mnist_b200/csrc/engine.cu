@@ -121,6 +121,7 @@ struct pdm_engine {
   uint64_t place_clock = 0;
   int32_t* idx_dev = nullptr;             // index plan of the current pass
   int64_t idx_cap = 0;
+  uint8_t* tc_ring = nullptr;             // feeder ring of the persistent tensor-core kernel (zero-copy placements)
   int32_t* idx_host = nullptr;            // pinned staging of the plan (so its upload is truly asynchronous)
   int64_t idx_host_cap = 0;
   // worker pool
@@ -658,6 +659,8 @@ int pdm_engine_place_dataset(pdm_engine* e, const uint8_t* images, const uint8_t
     p.host_labels = labels;
     PDM_CHECK_CUDA(cudaHostGetDevicePointer((void**)&p.images, const_cast<uint8_t*>(images), 0));
     PDM_CHECK_CUDA(cudaHostGetDevicePointer((void**)&p.labels, const_cast<uint8_t*>(labels), 0));
+    if (e->tc_ring == nullptr && pdm_net_tc_supported(e->device) == 1)      // feeder ring: allocated here, not inside a pass
+      PDM_CHECK_CUDA(cudaMalloc((void**)&e->tc_ring, PDM_TC_RING_BYTES));
   }
   p.n = n;
   p.last_use = e->place_clock;
@@ -736,6 +739,11 @@ int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, 
     t.metrics = e->metrics;
     t.step_out = e->host_results_dev;
     t.hyper = *hyper;
+    if (pl.mode == 1) {                     // rows come over PCIe: let the feeder cluster fetch them whole
+      if (e->tc_ring == nullptr) PDM_CHECK_CUDA(cudaMalloc((void**)&e->tc_ring, PDM_TC_RING_BYTES));
+      t.ring = e->tc_ring;
+      t.ring_bytes = PDM_TC_RING_BYTES;
+    }
     if (e->comm != nullptr) {
       rc = pdm_comm_peers_block(e->comm, &t.peers, nsteps);
       if (rc != PDM_OK) return rc;
@@ -834,6 +842,7 @@ int pdm_engine_destroy(pdm_engine* e) {
   if (e->ev_end) cudaEventDestroy(e->ev_end);
   if (e->host_results) cudaFreeHost(e->host_results);
   unplace_all(e);
+  if (e->tc_ring) cudaFree(e->tc_ring);
   if (e->idx_dev) cudaFree(e->idx_dev);
   if (e->idx_host) cudaFreeHost(e->idx_host);
   if (e->scratch) cudaFree(e->scratch);

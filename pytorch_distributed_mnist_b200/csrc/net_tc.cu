@@ -84,6 +84,10 @@ constexpr int kTraceSteps = 64;
 constexpr uint32_t kSmemBytes = kOffTrace + kTraceSteps * 32 * 8;
 constexpr uint32_t kTmemCols = 256;          // forward: 4 M-tiles x 48 columns, wgrad: 48 columns at column 192
 constexpr uint32_t kTmemWg = 192;
+// feeder ring: one slot = 512 rows of 784 bytes + 512 labels
+constexpr int kRingSlots = PDM_TC_RING_SLOTS;
+constexpr size_t kRingSlotBytes = PDM_TC_RING_SLOT_BYTES;
+static_assert(kRingSlotBytes == (size_t)kBlkRows * kIn + kBlkRows, "ring slot size");
 
 struct Misc {                     // lives at kOffMisc
   uint64_t bar_xfull, bar_fwd, bar_dl, bar_wg, bar_wop, bar_p1, bar_p2, bar_loss;
@@ -117,6 +121,8 @@ struct TcArgs {
   int opt;
   float lr, beta1, beta2, eps, wd;
   long long step0;                // 1-based index of the first update
+  uint8_t* ring;                  // optional device ring of kRingSlots blocks (rows + labels): the feeder cluster fills it
+  uint32_t* ring_flags;           // [2][kRingSlots]: blocks made ready (x13 per fill) / consumed (x13 per use)
   const float2* adam;             // per step of this launch: {lr / (1 - beta1^t), 1 / sqrt(1 - beta2^t)} (host-computed, double precision)
   float inv_world;
   int dbg;                        // bring-up switches (PDM_TC_DBG bit mask); 0 in production
@@ -317,6 +323,21 @@ __device__ __forceinline__ uint4 ld_stream16(const uint8_t* p) {
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
   return r;
 }
+// ring data was written by another SM during this kernel: read it through L2, never through the
+// non-coherent path
+__device__ __forceinline__ uint4 ld_l2_16(const uint8_t* p) {
+  uint4 r;
+  asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void flag_wait_ge(const uint32_t* flag, uint32_t target) {
+  while ((int32_t)(ld_acquire_gpu(flag) - target) < 0) __nanosleep(64);
+}
+__device__ __forceinline__ void flag_add_release(uint32_t* flag) {
+  __threadfence();
+  asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(flag) : "memory");
+}
 // four raw pixels -> four bf16 (exact), packed as two words.  No int->float conversion instruction
 // (quarter rate): 0x4B000000 | b is the float 8388608 + b, one full-rate FADD gives float(b), whose
 // upper 16 bits are its bf16.
@@ -346,20 +367,37 @@ __device__ __forceinline__ void producer_loop(const TcArgs& a, uint8_t* smem, Mi
       const Rows rows = block_rows(a, step, blk);
       constexpr int kItems = (kBlkRows * 4 + kProdThreads - 1) / kProdThreads;   // 10
       uint4 raw[kItems];
+      uint32_t lab[3];                                         // labels travel with the tile (three rows per thread)
+      const uint8_t* slot = nullptr;
+      if (a.ring != nullptr) {
+        // fed mode: the feeder cluster has gathered whole rows (large PCIe reads) into a device ring slot;
+        // this CTA picks its 64-byte column slices out of it through L2
+        if (pt == 0) flag_wait_ge(a.ring_flags + (it % kRingSlots), (uint32_t)kCtas * (it / kRingSlots + 1));
+        asm volatile("bar.sync 2, 224;" ::: "memory");
+        slot = a.ring + (size_t)(it % kRingSlots) * kRingSlotBytes;
+      }
 #pragma unroll
       for (int j = 0; j < kItems; ++j) {
         const int item = pt + kProdThreads * j;
         const int r = item >> 2, q = item & 3;
         raw[j] = make_uint4(0u, 0u, 0u, 0u);
         if (r < b.rows && q * 16 < valid_cols)
-          raw[j] = ld_stream16(a.x + rows(r) * kIn + col0 + q * 16);
+          raw[j] = slot != nullptr ? ld_l2_16(slot + (size_t)r * kIn + col0 + q * 16)
+                                   : ld_stream16(a.x + rows(r) * kIn + col0 + q * 16);
       }
-      uint32_t lab[3];                                         // labels travel with the tile (three rows per thread)
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
         const int r = pt + kProdThreads * j;
         lab[j] = 0u;
-        if (r < b.rows) lab[j] = min((uint32_t)__ldg(a.y + rows(r)), (uint32_t)(kOut - 1));
+        if (r < b.rows) {
+          if (slot != nullptr) {
+            uint32_t v;
+            asm volatile("ld.relaxed.gpu.global.u8 %0, [%1];" : "=r"(v) : "l"(slot + (size_t)kBlkRows * kIn + r) : "memory");
+            lab[j] = v;
+          } else {
+            lab[j] = min((uint32_t)__ldg(a.y + rows(r)), (uint32_t)(kOut - 1));
+          }
+        }
       }
       TC_TRACE(pt == 32, step, 16);
       if (it > 0) {                                            // previous block's MMAs are done with the tile
@@ -388,7 +426,69 @@ __device__ __forceinline__ void producer_loop(const TcArgs& a, uint8_t* smem, Mi
       }
       fence_async_smem();                                      // generic-proxy stores -> visible to the MMA (async proxy)
       mbar_arrive(&ms->bar_xfull);
+      if (a.ring != nullptr) {                                 // every producer thread has its slice in registers: the slot may be refilled
+        asm volatile("bar.sync 2, 224;" ::: "memory");
+        if (pt == 0) flag_add_release(a.ring_flags + kRingSlots + (it % kRingSlots));
+      }
       TC_TRACE(pt == 32, step, 18);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------- feeder cluster
+// A second cluster of the same launch (13 CTAs x 12 warps) walks the same block sequence a few blocks
+// ahead: every warp copies whole rows -- 784 contiguous bytes, i.e. full-size PCIe read requests when the
+// dataset is pinned host memory -- into a ring slot in device memory, labels behind the rows.  The slices
+// a trainer CTA needs (64 bytes of every row) would otherwise cross PCIe as 64-byte requests.
+__device__ __forceinline__ void feeder_loop(const TcArgs& a, int tid, int cta) {
+  const int warp = tid >> 5, lane = tid & 31;
+  constexpr int kWarps = kThreads / 32;                        // 12
+  uint32_t it = 0;
+  for (long long step = 0; step < a.nsteps; ++step) {
+    const int n_step = step_rows(a, step);
+    const int nblk = (n_step + kBlkRows - 1) / kBlkRows;
+    for (int blk = 0; blk < nblk; ++blk, ++it) {
+      const Blk b = make_blk(n_step, blk);
+      const Rows rows = block_rows(a, step, blk);
+      const uint32_t s = it % kRingSlots, gen = it / kRingSlots;
+      if (gen > 0) {                                           // the slot's previous block has been picked up by all 13 trainer CTAs
+        if (tid == 0) flag_wait_ge(a.ring_flags + kRingSlots + s, (uint32_t)kCtas * gen);
+        __syncthreads();
+      }
+      uint8_t* slot = a.ring + (size_t)s * kRingSlotBytes;
+      const int per = (b.rows + kCtas - 1) / kCtas;            // rows of this CTA
+      const int lo = cta * per, hi = min(b.rows, lo + per);
+      constexpr int kRowsPerWarp = 4;                          // rows in flight per warp (8 x 16 bytes per lane)
+      for (int r0 = lo + warp * kRowsPerWarp; r0 < hi; r0 += kWarps * kRowsPerWarp) {
+        uint4 v0[kRowsPerWarp], v1[kRowsPerWarp];
+        uint32_t yv[kRowsPerWarp];
+#pragma unroll
+        for (int k = 0; k < kRowsPerWarp; ++k) {
+          const int r = r0 + k;
+          v0[k] = v1[k] = make_uint4(0u, 0u, 0u, 0u);
+          yv[k] = 0u;
+          if (r < hi) {
+            const long long id = rows(r);
+            const uint8_t* src = a.x + id * kIn;
+            v0[k] = ld_stream16(src + lane * 16);
+            if (lane < 17) v1[k] = ld_stream16(src + 512 + lane * 16);
+            if (lane == 0) yv[k] = min((uint32_t)__ldg(a.y + id), (uint32_t)(kOut - 1));
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < kRowsPerWarp; ++k) {
+          const int r = r0 + k;
+          if (r < hi) {
+            uint8_t* dst = slot + (size_t)r * kIn;
+            *reinterpret_cast<uint4*>(dst + lane * 16) = v0[k];
+            if (lane < 17) *reinterpret_cast<uint4*>(dst + 512 + lane * 16) = v1[k];
+            if (lane == 0) slot[(size_t)kBlkRows * kIn + r] = (uint8_t)yv[k];
+          }
+        }
+      }
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) flag_add_release(a.ring_flags + s);
     }
   }
 }
@@ -781,6 +881,10 @@ __global__ void __launch_bounds__(kThreads, 1) net_tc_kernel(const __grid_consta
   uint32_t cta;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta));
 
+  if (blockIdx.x >= kCtas) {              // second cluster of the launch: the feeder (only launched with a ring)
+    feeder_loop(a, tid, (int)cta);
+    return;
+  }
   // zero every operand buffer (padding rows / columns must hold finite values), then the ones column
   for (uint32_t i = tid; i < kSmemBytes / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0u, 0u, 0u, 0u);
   __syncthreads();
@@ -829,9 +933,9 @@ __global__ void __launch_bounds__(kThreads, 1) net_tc_kernel(const __grid_consta
 }  // namespace
 
 // ---------------------------------------------------------------------------- host side
-static void tc_launch_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, cudaStream_t stream) {
+static void tc_launch_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, cudaStream_t stream, int clusters = 1) {
   *cfg = cudaLaunchConfig_t{};
-  cfg->gridDim = dim3(kCtas);
+  cfg->gridDim = dim3(kCtas * clusters);
   cfg->blockDim = dim3(kThreads);
   cfg->dynamicSmemBytes = kSmemBytes;
   cfg->stream = stream;
@@ -920,6 +1024,9 @@ extern "C" int pdm_net_tc_run(const pdm_net_tc_args* g, pdm_stream_t stream) {
   PDM_REQUIRE(g != nullptr, PDM_ERR_ARG, "pdm_net_tc_run: args is NULL");
   PDM_REQUIRE(g->x && g->y && g->params, PDM_ERR_ARG, "pdm_net_tc_run: x, y and params are required");
   PDM_REQUIRE(((uintptr_t)g->x & 15) == 0, PDM_ERR_ARG, "pdm_net_tc_run: x must be 16-byte aligned");
+  PDM_REQUIRE(g->ring == nullptr || (((uintptr_t)g->ring & 255) == 0 && g->ring_bytes >= PDM_TC_RING_BYTES), PDM_ERR_ARG,
+              "pdm_net_tc_run: ring must be 256-byte aligned device memory of at least PDM_TC_RING_BYTES (%zu) bytes",
+              (size_t)PDM_TC_RING_BYTES);
   PDM_REQUIRE(g->batch >= 1, PDM_ERR_ARG, "pdm_net_tc_run: batch must be >= 1 (got %d)", g->batch);
   PDM_REQUIRE(g->nsteps >= 0, PDM_ERR_ARG, "pdm_net_tc_run: nsteps must be >= 0");
   const pdm_hyper& h = g->hyper;
@@ -983,6 +1090,11 @@ extern "C" int pdm_net_tc_run(const pdm_net_tc_args* g, pdm_stream_t stream) {
     a.step0 = h.step + done;
     a.inv_world = world > 1 ? 1.0f / (float)world : 1.0f;
     a.adam = adam_dev;
+    if (g->ring != nullptr && g->row_index != nullptr) {
+      a.ring = static_cast<uint8_t*>(g->ring);
+      a.ring_flags = reinterpret_cast<uint32_t*>(a.ring + (size_t)kRingSlots * kRingSlotBytes);
+      PDM_CHECK_CUDA(cudaMemsetAsync(a.ring_flags, 0, 2 * kRingSlots * sizeof(uint32_t), (cudaStream_t)stream));
+    }
     a.trace = tc_trace_buffer();
     a.peers = g->peers;
     a.peers.world = world;
@@ -1000,7 +1112,7 @@ extern "C" int pdm_net_tc_run(const pdm_net_tc_args* g, pdm_stream_t stream) {
     PDM_CHECK_CUDA(cudaMemcpyAsync(adam_dev, adam_host, (size_t)n * sizeof(float2), cudaMemcpyHostToDevice, (cudaStream_t)stream));
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
-    tc_launch_config(&cfg, attr, (cudaStream_t)stream);
+    tc_launch_config(&cfg, attr, (cudaStream_t)stream, a.ring != nullptr ? 2 : 1);
     void* params[] = {&a};
     PDM_CHECK_CUDA(cudaLaunchKernelExC(&cfg, (const void*)net_tc_kernel, params));
   }

@@ -64,7 +64,10 @@ class NetTcArgs(ctypes.Structure):
                 ('batch', ctypes.c_int32), ('nsteps', ctypes.c_int64),
                 ('params', c_void_p), ('m', c_void_p), ('v', c_void_p),
                 ('grad_out', c_void_p), ('logits_out', c_void_p), ('metrics', c_void_p), ('step_out', c_void_p),
-                ('hyper', Hyper), ('peers', Peers)]
+                ('hyper', Hyper), ('peers', Peers), ('ring', c_void_p), ('ring_bytes', c_size_t)]
+
+
+TC_RING_BYTES = 4 * (512 * 784 + 512) + 256
 
 
 class NativeError(RuntimeError):

@@ -24,11 +24,12 @@ def supported(device=None):
 
 
 def tc_run(x, y, params, m, v, hyper, batch, nsteps=0, row_index=None, count=None, first_batch=0,
-           grad_out=None, logits_out=None, metrics=None, step_out=None, peers=None):
+           grad_out=None, logits_out=None, metrics=None, step_out=None, peers=None, ring=None):
     """x [N,784] uint8 and y [N] uint8 (device tensors, or pinned + mapped host memory given as
     ``(data_ptr, rows)`` tuples); params/m/v flat PDM_NET_FLAT float32.  Pool mode (``row_index`` None):
     step i reads batch ``(first_batch + i) % (N // batch)``.  Plan mode: ``row_index`` int32 device tensor,
-    ``count`` samples (default: all of it), last step ragged."""
+    ``count`` samples (default: all of it), last step ragged.  ``ring``: optional uint8 device tensor of
+    ``_lib.TC_RING_BYTES`` bytes that enables the feeder cluster (whole-row gather into a device ring)."""
     a = _lib.NetTcArgs()
     if isinstance(x, tuple):
         a.x, rows = x
@@ -51,4 +52,6 @@ def tc_run(x, y, params, m, v, hyper, batch, nsteps=0, row_index=None, count=Non
     a.hyper = hyper
     if peers is not None:
         a.peers = peers
+    if ring is not None:
+        a.ring, a.ring_bytes = ring.data_ptr(), ring.numel()
     _lib.check(_lib.lib().pdm_net_tc_run(ctypes.byref(a), _lib.stream_ptr()), 'pdm_net_tc_run')

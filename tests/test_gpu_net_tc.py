@@ -166,18 +166,46 @@ def test_rows_from_pinned_host_memory():
     idx = torch.randperm(n, generator=torch.Generator().manual_seed(2))[:count].to(torch.int32).to(dev)
     params = _params(17)
     h = _l.Hyper(opt=_l.PDM_OPT_ADAM, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0, step=1)
+    ring = torch.empty(_l.TC_RING_BYTES, dtype=torch.uint8, device=dev)
     res = []
-    for src in ('host', 'device'):
+    for src in ('host', 'host+feeder', 'device', 'device+feeder'):
         pd, m, v = params.to(dev), torch.zeros(7852, device=dev), torch.zeros(7852, device=dev)
         so = torch.zeros(count // B, 2, device=dev)
-        if src == 'host':
-            net_tc.tc_run((xp.data_ptr(), n), (yp.data_ptr(), n), pd, m, v, h, B, row_index=idx, step_out=so)
+        kw = dict(row_index=idx, step_out=so, ring=ring if 'feeder' in src else None)
+        if src.startswith('host'):
+            net_tc.tc_run((xp.data_ptr(), n), (yp.data_ptr(), n), pd, m, v, h, B, **kw)
         else:
-            net_tc.tc_run(x.to(dev), y.to(dev), pd, m, v, h, B, row_index=idx, step_out=so)
+            net_tc.tc_run(x.to(dev), y.to(dev), pd, m, v, h, B, **kw)
+        torch.cuda.synchronize()
+        res.append((pd.cpu(), so.cpu()))
+    # the feeder cluster (whole rows gathered into a device ring by a second cluster of the same launch)
+    # changes how bytes travel, not what is computed: all four runs are bit-identical
+    for r in res[1:]:
+        assert torch.equal(res[0][0], r[0]) and torch.equal(res[0][1], r[1])
+    assert not torch.equal(res[0][0], params)
+
+
+def test_feeder_ring_with_ragged_and_long_batches():
+    """Feeder mode over more blocks than ring slots, with a batch longer than one 512-row block and a ragged tail."""
+    _l, net_tc = _lib()
+    dev = torch.device('cuda', 0)
+    n, B, count = 6000, 700, 5000
+    x, y = _data(n, 41)
+    xp, yp = x.pin_memory(), y.pin_memory()
+    idx = torch.randperm(n, generator=torch.Generator().manual_seed(4))[:count].to(torch.int32).to(dev)
+    params = _params(19)
+    h = _l.Hyper(opt=_l.PDM_OPT_ADAM, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0, step=1)
+    ring = torch.empty(_l.TC_RING_BYTES, dtype=torch.uint8, device=dev)
+    nsteps = (count + B - 1) // B
+    res = []
+    for use_ring in (False, True):
+        pd, m, v = params.to(dev), torch.zeros(7852, device=dev), torch.zeros(7852, device=dev)
+        so = torch.zeros(nsteps, 2, device=dev)
+        net_tc.tc_run((xp.data_ptr(), n), (yp.data_ptr(), n), pd, m, v, h, B, row_index=idx, step_out=so,
+                      ring=ring if use_ring else None)
         torch.cuda.synchronize()
         res.append((pd.cpu(), so.cpu()))
     assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
-    assert not torch.equal(res[0][0], params)
 
 
 def test_engine_uses_the_persistent_kernel():
