@@ -61,6 +61,7 @@ struct Links {
   int world, rank;
   uint32_t epoch;
   uint64_t timeout_ns;
+  uint32_t skew_ns;              // fault injection (PDM_SKEW_NS): random pause before every flag this rank raises
   uint8_t* base[PDM_MAX_RANKS];  // region base of every rank, as mapped here
 };
 
@@ -72,6 +73,7 @@ __device__ __forceinline__ uint32_t* flag_word(const Links& L, int owner, int ki
 // Call after a CTA/grid barrier that orders the data writes before it.
 __device__ __forceinline__ void signal_peers(const Links& L, int kind) {
   if ((int)threadIdx.x < L.world) {
+    pdm_skew(L.skew_ns, L.epoch, (uint32_t)(L.rank * 8 + threadIdx.x), (uint32_t)kind);
     __threadfence_system();
     st_release_sys(flag_word(L, threadIdx.x, kind, L.rank), L.epoch);
   }
@@ -244,6 +246,7 @@ static Links make_links(pdm_comm* c) {
   if (c->epoch == 0) c->epoch = 1;
   L.epoch = c->epoch;
   L.timeout_ns = c->timeout_ns;
+  L.skew_ns = pdm_skew_ns();
   for (int p = 0; p < c->world; ++p) L.base[p] = c->base[p];
   return L;
 }

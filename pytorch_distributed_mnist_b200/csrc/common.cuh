@@ -13,6 +13,7 @@
 // error plumbing
 // ---------------------------------------------------------------------------
 void pdm_set_error(const char* fmt, ...);
+unsigned pdm_skew_ns(void);   /* PDM_SKEW_NS, read once */
 
 #define PDM_CHECK_CUDA(expr)                                                          \
   do {                                                                                \
@@ -86,6 +87,16 @@ __device__ __forceinline__ bool ll_load2(const uint64_t* src, uint32_t flag, flo
   a = __uint_as_float((uint32_t)u0);
   b = __uint_as_float((uint32_t)u1);
   return ((uint32_t)(u0 >> 32) == flag) && ((uint32_t)(u1 >> 32) == flag);
+}
+
+// Fault-injection aid for the cross-GPU flag protocols (PDM_SKEW_NS=<max ns>, default off): a pseudo-random
+// pause that differs per rank, CTA, thread and collective, placed right before a rank publishes data or
+// flags, so that soak runs (benchmarks/soak.py) exercise orderings an idle machine never produces.
+__device__ __forceinline__ void pdm_skew(uint32_t max_ns, uint32_t a, uint32_t b, uint32_t c) {
+  if (max_ns == 0) return;
+  uint32_t h = a * 2654435761u ^ (b + 0x9e3779b9u) * 40503u ^ (c * 2246822519u);
+  h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+  __nanosleep(h % max_ns);
 }
 
 #endif  // __CUDACC__

@@ -12,6 +12,12 @@ void pdm_set_error(const char* fmt, ...) {
 
 extern "C" const char* pdm_last_error(void) { return g_err; }
 
+#include <stdlib.h>
+unsigned pdm_skew_ns(void) {
+  static const unsigned v = [] { const char* e = getenv("PDM_SKEW_NS"); return e && *e ? (unsigned)atoi(e) : 0u; }();
+  return v;
+}
+
 extern "C" int pdm_version(void) { return 100; }
 
 extern "C" int pdm_device_ok(int device) {

@@ -88,6 +88,7 @@ struct KernelArgs {
   int trigger_early;      // 1: release the next step's launch as soon as this grid is resident
   int poll_ns;            // back-off between polls of sync[2]
   int ll_pull;            // 1: publish into our own outbox and read the peers' outboxes over NVLink
+  uint32_t skew_ns;       // fault injection (PDM_SKEW_NS): random pause before the LL publish
   int inputs_stable;      // 1: x / y / row_index were not written by the kernel just before this one on the
                           //    stream, so the first tile may be loaded before the dependency wait
   OptConsts oc;
@@ -505,6 +506,7 @@ __global__ void __launch_bounds__(kThreads, 1) net_kernel(const __grid_constant_
       // lanes' values, identically on every rank.
       const size_t par = (size_t)(seq & 1u) * W;
       const bool remote = valid && sub < W && sub != a.peers.rank;
+      pdm_skew(a.skew_ns, seq, (uint32_t)(a.peers.rank * 256 + cta), (uint32_t)(tid >> 5));
       // push (default): write our value into slot `rank` of every peer's inbox, poll our own inbox.
       // pull (PDM_NET_LL=pull): write it once into slot `rank` of OUR inbox and poll slot `sub` of
       // peer `sub`'s inbox over NVLink: a round trip per poll instead of a one-way store, but the
@@ -743,6 +745,7 @@ void apply_knobs(KernelArgs* ka, const pdm_net_step_args* args, int world, bool 
   ka->trigger_early = (ka->flag_wait && early) ? 1 : 0;
   ka->poll_ns = poll;
   ka->ll_pull = pull_env >= 0 ? pull_env : (world > 1 ? 1 : 0);
+  ka->skew_ns = pdm_skew_ns();
 }
 
 }  // namespace

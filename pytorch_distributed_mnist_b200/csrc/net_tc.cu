@@ -125,6 +125,7 @@ struct TcArgs {
   uint32_t* ring_flags;           // [2][kRingSlots]: blocks made ready (x13 per fill) / consumed (x13 per use)
   const float2* adam;             // per step of this launch: {lr / (1 - beta1^t), 1 / sqrt(1 - beta2^t)} (host-computed, double precision)
   float inv_world;
+  uint32_t skew_ns;               // fault injection: random pause (< skew_ns) before this rank publishes its gradient
   int dbg;                        // bring-up switches (PDM_TC_DBG bit mask); 0 in production
   long long* trace;               // optional [13][kTraceSteps][32] clock64 stamps per CTA (PDM_TC_TRACE=1)
   pdm_peers peers;
@@ -546,6 +547,7 @@ constexpr int kLLSlot = 65 * kOut;      // units per (parity, source rank, CTA)
 __device__ __forceinline__ void ll_exchange(const TcArgs& a, uint32_t seq, int cta, int t, float (&g)[kOut]) {
   const int W = a.peers.world, me = a.peers.rank;
   const size_t par = (size_t)(seq & 1u) * W;
+  pdm_skew(a.skew_ns, seq, (uint32_t)(me * 16 + cta), (uint32_t)(t >> 5));
   for (int p = 0; p < W; ++p) {
     if (p == me) continue;
     uint64_t* dst = a.peers.inbox[p] + ((par + me) * kCtas + cta) * kLLSlot + (size_t)t * kOut;
@@ -1090,6 +1092,7 @@ extern "C" int pdm_net_tc_run(const pdm_net_tc_args* g, pdm_stream_t stream) {
     a.step0 = h.step + done;
     a.inv_world = world > 1 ? 1.0f / (float)world : 1.0f;
     a.adam = adam_dev;
+    a.skew_ns = pdm_skew_ns();
     if (g->ring != nullptr && g->row_index != nullptr) {
       a.ring = static_cast<uint8_t*>(g->ring);
       a.ring_flags = reinterpret_cast<uint32_t*>(a.ring + (size_t)kRingSlots * kRingSlotBytes);
