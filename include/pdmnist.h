@@ -329,6 +329,7 @@ typedef struct pdm_cnn_params {
   float *conv1_w, *conv1_b, *conv2_w, *conv2_b, *fc1_w, *fc1_b, *fc2_w, *fc2_b;
 } pdm_cnn_params;
 struct pdm_comm;
+struct pdm_nvls;
 typedef struct pdm_cnn_plan {
   int32_t n_buckets;            /* 1..4, in launch order (bucket 0 = the LAST parameters) */
   int32_t max_ctas;             /* CTAs for each reducer kernel (0 = default) */
@@ -338,6 +339,8 @@ typedef struct pdm_cnn_plan {
   float *params, *grads, *m, *v;                /* comm == NULL: the flat buffers themselves */
   pdm_hyper hyper;
   float grad_scale;             /* 1/world */
+  struct pdm_nvls* nvls;        /* non-NULL: the flat buffers live in this NVLS region (offsets as above, into ITS data
+                                   area) and every bucket is reduced in the switch (pdm_nvls_allreduce_optim) */
 } pdm_cnn_plan;
 int pdm_cnn_create(pdm_cnn_ctx** out, int device, int width, int max_batch);
 int pdm_cnn_eval_step(pdm_cnn_ctx* c, const void* x, int x_dtype, const void* y, int y_dtype, int batch,
@@ -390,8 +393,10 @@ int pdm_comm_allreduce_optim(pdm_comm* c, size_t grad_off, size_t out_off, size_
 int pdm_comm_destroy(pdm_comm* c);
 
 /* ------------------------------------------------------------------------
- * NVLS (multicast / multimem) region (nvls.cu).  EXPERIMENTAL: compiled, not yet
- * run on hardware in round 1; nothing uses it unless asked (parallel/nvls.py).
+ * NVLS (multicast / multimem) region (nvls.cu): the in-switch path NCCL takes for large
+ * all-reduces.  The reducer uses it for models of >= 8 MB at 4 or more GPUs
+ * (parallel/ddp.py; PDM_NVLS=0 / 1 forces it off / on); it moves 1 + 1/W of the payload per GPU
+ * and direction where the peer-memory two-shot kernel moves 2 (W-1)/W.
  * A symmetric region of VMM memory bound to a multicast object, so that
  * `multimem.ld_reduce` sums an address over all replicas inside the NVSwitch and
  * `multimem.st` writes all replicas with one store.  Bootstrap, in order:

@@ -184,6 +184,10 @@ int pdm_cnn_train_step(pdm_cnn_ctx* c, const void* x, int x_dtype, const void* y
     PDM_CHECK_CUDA(cudaEventRecord(c->ev_bucket[b & 1], s));
     PDM_CHECK_CUDA(cudaStreamWaitEvent(c->comm_stream, c->ev_bucket[b & 1], 0));
     const size_t lo = (size_t)plan->lo[b], n = (size_t)(plan->hi[b] - plan->lo[b]);
+    if (plan->nvls != nullptr) {
+      return pdm_nvls_allreduce_optim(plan->nvls, plan->grads_off + lo * 4, plan->params_off + lo * 4, plan->m_off + lo * 4,
+                                      plan->v_off + lo * 4, n, &plan->hyper, plan->grad_scale, c->comm_stream);
+    }
     if (plan->comm != nullptr) {
       return pdm_comm_allreduce_optim(plan->comm, plan->grads_off + lo * 4, plan->params_off + lo * 4, plan->m_off + lo * 4,
                                       plan->v_off + lo * 4, n, &plan->hyper, plan->grad_scale, 0, plan->max_ctas, c->comm_stream);

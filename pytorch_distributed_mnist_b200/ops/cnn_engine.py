@@ -34,7 +34,7 @@ class CnnPlan(ctypes.Structure):
                 ('params_off', ctypes.c_size_t), ('grads_off', ctypes.c_size_t),
                 ('m_off', ctypes.c_size_t), ('v_off', ctypes.c_size_t),
                 ('params', c_void_p), ('grads', c_void_p), ('m', c_void_p), ('v', c_void_p),
-                ('hyper', _lib.Hyper), ('grad_scale', ctypes.c_float)]
+                ('hyper', _lib.Hyper), ('grad_scale', ctypes.c_float), ('nvls', c_void_p)]
 
 
 @_lib.optional_decl('pdm_cnn_create')
@@ -99,6 +99,7 @@ class CnnEngine(object):
         self._ranges = ranges
         self.world = getattr(ddp, 'world', 1) if ddp is not None else 1
         self.comm = ddp.comm if (ddp is not None and getattr(ddp, 'uses_peer', False)) else None
+        self.nvls = getattr(ddp, 'nvls', None) if ddp is not None else None
         if self.world > 1 and self.comm is None:
             raise RuntimeError('CnnEngine needs the peer communicator for multi-GPU jobs')
 
@@ -109,7 +110,14 @@ class CnnEngine(object):
         plan.max_ctas = 0
         for i, (lo, hi) in enumerate(self._ranges):
             plan.lo[i], plan.hi[i] = lo, hi
-        if self.comm is not None:
+        if self.nvls is not None:            # flat buffers live in the multicast region: reduce in the switch
+            plan.nvls = self.nvls._h
+            plan.comm = None
+            plan.params_off = self.nvls.offset_of(flat.params)
+            plan.grads_off = self.nvls.offset_of(flat.grads)
+            plan.m_off = self.nvls.offset_of(flat.exp_avg)
+            plan.v_off = self.nvls.offset_of(flat.exp_avg_sq)
+        elif self.comm is not None:
             plan.comm = self.comm.handle
             plan.params_off = self.comm.offset_of(flat.params)
             plan.grads_off = self.comm.offset_of(flat.grads)
@@ -138,7 +146,7 @@ class CnnEngine(object):
         plan = self._plan()
         if self.comm is not None:
             for lo, hi in self._ranges:          # buckets >= 256 KB take the two-shot kernel: state is slice-wise
-                self.flat.mark_sharded(lo, hi, self.world)
+                self.flat.mark_sharded(lo, hi, self.world, force=self.nvls is not None)
         train = self.cnn.training
         _lib.check(self._lib.pdm_cnn_train_step(
             self._h, x.data_ptr(), _lib.dtype_code(x), y.data_ptr(), _lib.dtype_code(y), x.size(0),

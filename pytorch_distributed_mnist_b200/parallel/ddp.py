@@ -45,6 +45,7 @@ from .peer import GroupComm, PeerComm
 
 FIRST_BUCKET_BYTES = 1024 * 1024          # torch's _DEFAULT_FIRST_BUCKET_BYTES
 DEFAULT_BUCKET_CAP_MB = 25
+NVLS_MIN_BYTES = 8 * 1024 * 1024           # models at least this big reduce in the switch (>= 4 GPUs)
 
 
 def assign_buckets(numels, first_cap_bytes=FIRST_BUCKET_BYTES, cap_bytes=DEFAULT_BUCKET_CAP_MB * 1024 * 1024,
@@ -149,10 +150,30 @@ class DistributedDataParallel(nn.Module):
         if self.comm is None:
             self.comm = GroupComm(process_group)
 
+        # -- in-switch reduction (NVLS) for large models at >= 4 GPUs ---------
+        # The multimem kernel moves 1 + 1/W of a bucket per GPU and direction, the peer-memory two-shot
+        # kernel 2 (W-1)/W: a win from 4 GPUs on (measured: profiles/README.md), a loss at 2.
+        # PDM_NVLS=0 / 1 forces the choice.
+        self.nvls = None
+        if self.uses_peer and self.world > 1:
+            import os
+            from .nvls import NvlsRegion
+            want = os.environ.get('PDM_NVLS', '')
+            auto = self.world >= 4 and section * 4 >= NVLS_MIN_BYTES
+            if want != '0' and (want == '1' or auto) and NvlsRegion.supported(self.device.index or 0):
+                self.nvls = NvlsRegion(self.rank, self.world, self.device,
+                                       data_bytes=section * 4 * len(FlatState.SECTIONS) + 4096,
+                                       store=store, timeout_s=comm_timeout_s)
+
         # -- flat storage, verification, initial broadcast -------------------
-        self.flat = FlatState(params, device=self.device, comm=self.comm if self.uses_peer else None)
+        self.flat = FlatState(params, device=self.device,
+                              comm=self.nvls if self.nvls is not None else (self.comm if self.uses_peer else None))
         self._verify_params(params, process_group)
-        self.comm.broadcast(self.flat.params, root=0)
+        if self.nvls is not None:
+            if self.world > 1:
+                dist.broadcast(self.flat.params, 0, group=process_group)     # one-off; the region is not IPC-mapped
+        else:
+            self.comm.broadcast(self.flat.params, root=0)
         for b in module.buffers():
             if self.world > 1:
                 dist.broadcast(b, 0, group=process_group)
@@ -281,11 +302,18 @@ class DistributedDataParallel(nn.Module):
             cs = self.comm_stream
             cs.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(cs):
-                if opt is not None:
+                if opt is not None and self.nvls is not None:
+                    h = opt.hyper(opt.step_count + 1)
+                    flat.mark_sharded(lo, hi, self.world, force=True)      # rank r updates slice r of every bucket
+                    self.nvls.allreduce_optim(flat.grads[lo:hi], flat.params[lo:hi], flat.exp_avg[lo:hi],
+                                              flat.exp_avg_sq[lo:hi], h, stream=cs)
+                elif opt is not None:
                     h = opt.hyper(opt.step_count + 1)
                     flat.mark_sharded(lo, hi, self.world)      # >= 256 KB: two-shot, state updated slice-wise
                     self.comm.allreduce_optim(flat.grads[lo:hi], flat.params[lo:hi], flat.exp_avg[lo:hi],
                                               flat.exp_avg_sq[lo:hi], h, stream=cs)
+                elif self.nvls is not None:
+                    self.nvls.allreduce(flat.grads[lo:hi], flat.grads[lo:hi], average=True, stream=cs)
                 elif self.world > 1:
                     self.comm.allreduce(flat.grads[lo:hi], flat.grads[lo:hi], average=True, algo=2, stream=cs)
             if opt is not None and b == len(self.buckets) - 1:
@@ -322,5 +350,8 @@ class DistributedDataParallel(nn.Module):
         for h in self._hooks:
             h.remove()
         self._hooks = []
+        if self.nvls is not None:
+            self.nvls.close()
+            self.nvls = None
         if self.comm is not None:
             self.comm.close()

@@ -110,9 +110,10 @@ class FlatState(object):
         b = min(n4, a + per)
         return lo + 4 * a, lo + 4 * b
 
-    def mark_sharded(self, lo, hi, world):
-        """Record that the fused update of floats [lo, hi) runs slice-wise over ``world`` ranks."""
-        if world > 1 and 4 * (hi - lo) >= TWO_SHOT_MIN_BYTES:
+    def mark_sharded(self, lo, hi, world, force=False):
+        """Record that the fused update of floats [lo, hi) runs slice-wise over ``world`` ranks
+        (``force``: the in-switch kernel slices every bucket, whatever its size)."""
+        if world > 1 and (force or 4 * (hi - lo) >= TWO_SHOT_MIN_BYTES):
             self.sharded[(int(lo), int(hi))] = int(world)
             self.state_stale = True
 

@@ -214,14 +214,17 @@ def test_persistent_tc_kernel_ll_allreduce(free_port):
     mp.spawn(_tc_worker, args=(_world(), free_port), nprocs=_world())
 
 
-def _cnn_worker(rank, world, port, native=False):
+def _cnn_worker(rank, world, port, native=False, nvls=False):
     import pytorch_distributed_mnist_b200 as pdm
+    if nvls:
+        os.environ['PDM_NVLS'] = '1'          # reduce every bucket in the switch (normally: >= 4 GPUs, >= 8 MB)
     _init(rank, world, port)
     try:
         dev = torch.device('cuda', rank)
         torch.manual_seed(7 + rank)
         ours = pdm.DistributedDataParallel(pdm.CNN().to(dev), device_ids=[rank])
         assert ours.uses_peer and len(ours.buckets) >= 2
+        assert (ours.nvls is not None) == bool(nvls)
         torch.manual_seed(7)
         stock_mod = pdm.CNN().to(dev)
         stock = torch.nn.parallel.DistributedDataParallel(stock_mod, device_ids=[rank])
@@ -286,6 +289,20 @@ def test_native_cnn_step_multi_gpu(free_port):
     """csrc/cnn_step.cu driving the per-bucket fused all-reduce + Adam: same parameters as stock
     DDP + torch.optim.Adam after 4 steps, bit-identical replicas."""
     mp.spawn(_cnn_worker, args=(_world(), free_port, True), nprocs=_world())
+
+
+def _nvls_ok():
+    from pytorch_distributed_mnist_b200.parallel.nvls import NvlsRegion
+    return NvlsRegion.supported(0)
+
+
+@pytest.mark.parametrize('native', [False, True])
+def test_cnn_reducer_in_the_switch(free_port, native):
+    """The same two CNN checks with the flat buffers in the multicast region and every bucket reduced by
+    the multimem kernel (autograd hooks path, then the native step executor)."""
+    if not _nvls_ok():
+        pytest.skip('no multicast (NVLS) support on this box')
+    mp.spawn(_cnn_worker, args=(_world(), free_port, native, True), nprocs=_world())
 
 
 def _run_worker(rank, world, port, out_dir):
