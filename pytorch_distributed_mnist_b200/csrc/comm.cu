@@ -39,7 +39,7 @@
 
 namespace {
 
-constexpr size_t kLLBytes = 2u << 20;  // >= 2 * 8 * 1963 * 32 (net_step.cu) and >= 2 * 8 * 13 * 650 * 8 (net_tc.cu)
+constexpr size_t kLLBytes = 2u << 20;  // >= 2 * 8 * 1963 * 32 (net_step.cu) and >= 2 * 8 * 13 * 960 * 8 (net_tc.cu)
 constexpr size_t kFlagBytes = 4096;
 constexpr size_t kHeaderBytes = kLLBytes + kFlagBytes;
 constexpr int kFlagStart = 0;   // word offsets inside the flag block (32 words = 128 B apart)

@@ -543,16 +543,19 @@ __device__ __forceinline__ void mma_loop(const TcArgs& a, uint8_t* smem, Misc* m
 // They are pushed into every peer's inbox as 8-byte {value, flag} units and the peers' values are
 // polled from our own inbox; the sum is formed in rank order on every rank.  Two buffer halves
 // alternate by sequence parity (a rank can be at most one step ahead of any other).
-constexpr int kLLSlot = 65 * kOut;      // units per (parity, source rank, CTA)
+// Layout of one (parity, source rank, CTA) slot: [value pair 5][lane 96][2 units], so that one store
+// instruction of a warp covers 512 contiguous bytes (full NVLink packets) instead of 32 scattered 16-byte pieces.
+constexpr int kLLLanes = 96;
+constexpr int kLLSlot = (kOut / 2) * kLLLanes * 2;      // units per slot
 __device__ __forceinline__ void ll_exchange(const TcArgs& a, uint32_t seq, int cta, int t, float (&g)[kOut]) {
   const int W = a.peers.world, me = a.peers.rank;
   const size_t par = (size_t)(seq & 1u) * W;
   pdm_skew(a.skew_ns, seq, (uint32_t)(me * 16 + cta), (uint32_t)(t >> 5));
   for (int p = 0; p < W; ++p) {
     if (p == me) continue;
-    uint64_t* dst = a.peers.inbox[p] + ((par + me) * kCtas + cta) * kLLSlot + (size_t)t * kOut;
+    uint64_t* dst = a.peers.inbox[p] + ((par + me) * kCtas + cta) * kLLSlot + (size_t)t * 2;
 #pragma unroll
-    for (int i = 0; i < kOut; i += 2) ll_store2(dst + i, g[i], g[i + 1], seq);
+    for (int i = 0; i < kOut; i += 2) ll_store2(dst + (size_t)(i / 2) * (kLLLanes * 2), g[i], g[i + 1], seq);
   }
   float sum[kOut];
 #pragma unroll
@@ -563,14 +566,14 @@ __device__ __forceinline__ void ll_exchange(const TcArgs& a, uint32_t seq, int c
       for (int i = 0; i < kOut; ++i) sum[i] += g[i];
       continue;
     }
-    const uint64_t* src = a.peers.inbox[me] + ((par + p) * kCtas + cta) * kLLSlot + (size_t)t * kOut;
+    const uint64_t* src = a.peers.inbox[me] + ((par + p) * kCtas + cta) * kLLSlot + (size_t)t * 2;
     float q[kOut];
     uint32_t done = 0, spins = 0;
     uint64_t t0 = 0;
     while (done != 0x1Fu) {
 #pragma unroll
       for (int i = 0; i < kOut; i += 2)
-        if (!((done >> (i / 2)) & 1u) && ll_load2(src + i, seq, q[i], q[i + 1])) done |= 1u << (i / 2);
+        if (!((done >> (i / 2)) & 1u) && ll_load2(src + (size_t)(i / 2) * (kLLLanes * 2), seq, q[i], q[i + 1])) done |= 1u << (i / 2);
       if (done != 0x1Fu && (++spins & 1023u) == 0u && a.peers.timeout_ns != 0) {
         const uint64_t now = globaltimer_ns();
         if (t0 == 0) t0 = now;
