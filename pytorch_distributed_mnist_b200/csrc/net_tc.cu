@@ -75,9 +75,9 @@ constexpr uint32_t kOffXbuf = kOffWop + 3 * kWopSplitBytes;                 // p
 constexpr uint32_t kXbufBytes = kCtas * kOwnRows * kOut * 4;                // 20,800
 constexpr uint32_t kOffStage = kOffXbuf + kXbufBytes;                       // my partial logits of all rows [512][10] f32 (bulk-copy source)
 constexpr uint32_t kStageBytes = kBlkRows * kOut * 4;                       // 20,480
-constexpr uint32_t kOffZbuf = kOffStage + kStageBytes;                      // summed logits of my rows [40][10] f32
-constexpr uint32_t kZbufBytes = kOwnRows * kOut * 4;                        // 1,600
-constexpr uint32_t kOffMisc = kOffZbuf + kZbufBytes;
+constexpr uint32_t kOffGbuf = kOffStage + kStageBytes;                      // this CTA's gradient as LL units [325] float2 (multi-GPU exchange)
+constexpr uint32_t kGbufBytes = 2624;
+constexpr uint32_t kOffMisc = kOffGbuf + kGbufBytes;
 constexpr uint32_t kMiscBytes = 2048;
 constexpr uint32_t kOffTrace = kOffMisc + kMiscBytes;                       // [kTraceSteps][32] clock stamps (PDM_TC_TRACE=1)
 constexpr int kTraceSteps = 64;
@@ -539,55 +539,88 @@ __device__ __forceinline__ void mma_loop(const TcArgs& a, uint8_t* smem, Misc* m
 }
 
 // ---------------------------------------------------------------------------- LL exchange with the peer GPUs
-// Thread t <= 64 of CTA c holds 10 gradient values (one input column, or the bias for t == 64).
-// They are pushed into every peer's inbox as 8-byte {value, flag} units and the peers' values are
-// polled from our own inbox; the sum is formed in rank order on every rank.  Two buffer halves
-// alternate by sequence parity (a rank can be at most one step ahead of any other).
-// Layout of one (parity, source rank, CTA) slot: [value pair 5][lane 96][2 units], so that one store
-// instruction of a warp covers 512 contiguous bytes (full NVLink packets) instead of 32 scattered 16-byte pieces.
-constexpr int kLLLanes = 96;
-constexpr int kLLSlot = (kOut / 2) * kLLLanes * 2;      // units per slot
-__device__ __forceinline__ void ll_exchange(const TcArgs& a, uint32_t seq, int cta, int t, float (&g)[kOut]) {
+// A CTA's gradient is 65 value sets of 10 floats (64 input columns + the bias) = 325 16-byte LL units
+// ({value, flag} x 2).  They are staged in shared memory and ALL 128 epilogue threads push them into
+// every peer's inbox and poll the peers' units out of our own inbox -- consecutive threads handle
+// consecutive units of one peer (512 contiguous bytes per warp instruction), and the cost does not grow
+// with the number of peers the way one-owner-walks-its-peers did (20.6 -> us/step at 8 GPUs).  The
+// owners then add the peers' values in rank order, identically on every rank (bit-identical replicas).
+// Two buffer halves alternate by sequence parity (a rank can be at most one step ahead of any other).
+constexpr int kLLUnits = 65 * kOut / 2;     // 325 units of 16 bytes per (parity, source rank, CTA)
+constexpr int kLLSlot = kLLUnits * 2;       // in uint64
+__device__ __forceinline__ void ll_exchange(const TcArgs& a, uint8_t* smem, uint32_t seq, int cta, int t, float (&g)[kOut]) {
   const int W = a.peers.world, me = a.peers.rank;
   const size_t par = (size_t)(seq & 1u) * W;
-  pdm_skew(a.skew_ns, seq, (uint32_t)(me * 16 + cta), (uint32_t)(t >> 5));
-  for (int p = 0; p < W; ++p) {
-    if (p == me) continue;
-    uint64_t* dst = a.peers.inbox[p] + ((par + me) * kCtas + cta) * kLLSlot + (size_t)t * 2;
+  float2* gbuf = reinterpret_cast<float2*>(smem + kOffGbuf);               // [325] this CTA's units
+  float2* rbuf = reinterpret_cast<float2*>(smem + kOffStage);              // [W - 1][325] the peers' units (the staging buffer is only ever written by this CTA and is idle here)
+  if (t <= kCols) {
 #pragma unroll
-    for (int i = 0; i < kOut; i += 2) ll_store2(dst + (size_t)(i / 2) * (kLLLanes * 2), g[i], g[i + 1], seq);
+    for (int i = 0; i < kOut; i += 2) gbuf[t * (kOut / 2) + i / 2] = make_float2(g[i], g[i + 1]);
   }
-  float sum[kOut];
+  epi_sync();
+  pdm_skew(a.skew_ns, seq, (uint32_t)(me * 16 + cta), (uint32_t)(t >> 5));
+  const int total = (W - 1) * kLLUnits;
+  for (int idx = t; idx < total; idx += kEpiThreads) {
+    const int k = idx / kLLUnits, u = idx - k * kLLUnits;
+    const int p = k + (k >= me ? 1 : 0);
+    const float2 v = gbuf[u];
+    ll_store2(a.peers.inbox[p] + ((par + me) * kCtas + cta) * kLLSlot + (size_t)u * 2, v.x, v.y, seq);
+  }
+  // poll: up to four units in flight per thread and round
+  for (int idx0 = t; idx0 < total; idx0 += 4 * kEpiThreads) {
+    uint32_t pending = 0;
 #pragma unroll
-  for (int i = 0; i < kOut; ++i) sum[i] = 0.f;
-  for (int p = 0; p < W; ++p) {
-    if (p == me) {
-#pragma unroll
-      for (int i = 0; i < kOut; ++i) sum[i] += g[i];
-      continue;
-    }
-    const uint64_t* src = a.peers.inbox[me] + ((par + p) * kCtas + cta) * kLLSlot + (size_t)t * 2;
-    float q[kOut];
-    uint32_t done = 0, spins = 0;
+    for (int j = 0; j < 4; ++j) if (idx0 + j * kEpiThreads < total) pending |= 1u << j;
+    uint32_t spins = 0;
     uint64_t t0 = 0;
-    while (done != 0x1Fu) {
+    while (pending != 0u) {
 #pragma unroll
-      for (int i = 0; i < kOut; i += 2)
-        if (!((done >> (i / 2)) & 1u) && ll_load2(src + (size_t)(i / 2) * (kLLLanes * 2), seq, q[i], q[i + 1])) done |= 1u << (i / 2);
-      if (done != 0x1Fu && (++spins & 1023u) == 0u && a.peers.timeout_ns != 0) {
+      for (int j = 0; j < 4; ++j) {
+        if (!((pending >> j) & 1u)) continue;
+        const int idx = idx0 + j * kEpiThreads;
+        const int k = idx / kLLUnits, u = idx - k * kLLUnits;
+        const int p = k + (k >= me ? 1 : 0);
+        float x, y;
+        if (ll_load2(a.peers.inbox[me] + ((par + p) * kCtas + cta) * kLLSlot + (size_t)u * 2, seq, x, y)) {
+          rbuf[k * kLLUnits + u] = make_float2(x, y);
+          pending &= ~(1u << j);
+        }
+      }
+      if (pending != 0u && (++spins & 1023u) == 0u && a.peers.timeout_ns != 0) {
         const uint64_t now = globaltimer_ns();
         if (t0 == 0) t0 = now;
         else if (now - t0 > a.peers.timeout_ns) {
-          if (a.peers.status != nullptr) atomicExch(a.peers.status, 1 + p);
+          const int idx = idx0 + (__ffs(pending) - 1) * kEpiThreads;
+          const int k = idx / kLLUnits;
+          if (a.peers.status != nullptr) atomicExch(a.peers.status, 1 + k + (k >= me ? 1 : 0));
           break;
         }
       }
     }
-#pragma unroll
-    for (int i = 0; i < kOut; ++i) sum[i] += q[i];
   }
+  epi_sync();
+  if (t <= kCols) {
+    float sum[kOut];
 #pragma unroll
-  for (int i = 0; i < kOut; ++i) g[i] = sum[i];
+    for (int i = 0; i < kOut; ++i) sum[i] = 0.f;
+    for (int p = 0; p < W; ++p) {
+      if (p == me) {
+#pragma unroll
+        for (int i = 0; i < kOut; ++i) sum[i] += g[i];
+      } else {
+        const int k = p - (p > me ? 1 : 0);
+#pragma unroll
+        for (int i = 0; i < kOut; i += 2) {
+          const float2 v = rbuf[k * kLLUnits + t * (kOut / 2) + i / 2];
+          sum[i] += v.x;
+          sum[i + 1] += v.y;
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < kOut; ++i) g[i] = sum[i];
+  }
+  epi_sync();                                 // gbuf / rbuf are the next step's exchange buffers again
 }
 
 // Publish this thread's weights as the next forward's B operand (three bf16 terms, K-major 8x8
@@ -843,14 +876,14 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
       }
       epi_sync();
       TC_TRACE(t == 0, step, 21);
-      if (t <= kCols) {
-        float g[kOut];
+      float g[kOut];
 #pragma unroll
-        for (int n = 0; n < kOut; ++n) {
-          const float dbn = ms->db[n];
-          g[n] = is_bias ? dbn : (owns_col ? fmaf(kScale, gsum[n], -kShift * dbn) : 0.f);
-        }
-        if (a.peers.world > 1) ll_exchange(a, a.peers.seq + (uint32_t)step, cta, t, g);
+      for (int n = 0; n < kOut; ++n) {
+        const float dbn = ms->db[n];
+        g[n] = is_bias ? dbn : (owns_col ? fmaf(kScale, gsum[n], -kShift * dbn) : 0.f);
+      }
+      if (a.peers.world > 1) ll_exchange(a, smem, a.peers.seq + (uint32_t)step, cta, t, g);   // all 128 threads
+      if (t <= kCols) {
         const float step_size = adam_c.x, inv_bc2 = adam_c.y;
         const bool first = a.step0 + step <= 1;
         if (owns_col || is_bias) {
