@@ -83,6 +83,7 @@ struct pdm_engine {
   float* m = nullptr;
   float* v = nullptr;
   pdm_comm* comm = nullptr;
+  int world = 1;                          // ranks of `comm`
   // owned device memory
   float* scratch = nullptr;
   uint32_t* sync = nullptr;
@@ -216,9 +217,18 @@ void worker_main(pdm_engine* e) {
 // The persistent tensor-core kernel (net_tc.cu) takes a whole pass in one launch: used for raw uint8
 // inputs whenever the device can launch it and the caller did not ask for a specific CTA count.
 // It runs on one 13-SM cluster, so beyond ~1024 rows per step the 148-SM per-step kernel is faster
-// (measured: 8.3 vs 9.6 us at batch 512, 57 vs 27 us at batch 4096; benchmarks/tc_sweep.py).
-bool use_tc(const pdm_engine* e, int x_dtype, int y_dtype, int ctas, int batch) {
-  return x_dtype == PDM_U8 && y_dtype == PDM_U8 && ctas == 0 && batch <= 1024 && pdm_net_tc_supported(e->device) == 1;
+// (measured: 8.3 vs 9.6 us at batch 512, 57 vs 27 us at batch 4096; benchmarks/tc_sweep.py).  With peers its
+// in-kernel exchange wins up to PDM_NET_TC_MAX_WORLD GPUs (default 4; measured us/step: 2 GPUs 11.2 vs 12.7,
+// 4 GPUs 12.5 vs 14.0, 8 GPUs 17.9 vs 14.7) for resident inputs; passes that read pinned host memory always take it, for its feeder cluster
+// (8 GPUs: 21 vs 32 us/step).
+int tc_max_world() {
+  static const int v = [] { const char* e = getenv("PDM_NET_TC_MAX_WORLD"); return e && *e ? atoi(e) : 4; }();
+  return v;
+}
+bool use_tc(const pdm_engine* e, int x_dtype, int y_dtype, int ctas, int batch, bool from_host) {
+  if (!(x_dtype == PDM_U8 && y_dtype == PDM_U8 && ctas == 0 && batch <= 1024 && pdm_net_tc_supported(e->device) == 1)) return false;
+  if (from_host || e->comm == nullptr) return true;
+  return e->world <= tc_max_world();
 }
 
 int ensure_results(pdm_engine* e, int64_t nsteps) {
@@ -300,6 +310,11 @@ int pdm_engine_bind(pdm_engine* e, float* params, float* m, float* v, pdm_comm* 
   e->m = m;
   e->v = v;
   e->comm = comm;
+  e->world = 1;
+  if (comm != nullptr) {
+    pdm_peers pr;
+    if (pdm_comm_peers(comm, &pr, 0) == PDM_OK) e->world = pr.world > 1 ? pr.world : 1;
+  }
   return PDM_OK;
 }
 
@@ -515,7 +530,7 @@ int pdm_engine_run_device_typed(pdm_engine* e, const void* dev_images, int x_dty
   PDM_CHECK_CUDA(cudaSetDevice(e->device));
   const int64_t nb = pool_samples / batch;
   cudaStream_t st = e->stream[0];
-  if (nsteps >= 1 && use_tc(e, x_dtype, y_dtype, ctas, batch)) {
+  if (nsteps >= 1 && use_tc(e, x_dtype, y_dtype, ctas, batch, false)) {
     pdm_net_tc_args t;
     memset(&t, 0, sizeof(t));
     t.x = static_cast<const uint8_t*>(dev_images);
@@ -725,7 +740,7 @@ int pdm_engine_run_gather(pdm_engine* e, const int64_t* indices, int64_t count, 
   cudaStream_t cs = e->stream[0];
   PDM_CHECK_CUDA(cudaEventRecord(e->ev_begin, cs));
   PDM_CHECK_CUDA(cudaMemcpyAsync(e->idx_dev, e->idx_host, (size_t)count * sizeof(int32_t), cudaMemcpyHostToDevice, cs));
-  if (use_tc(e, PDM_U8, PDM_U8, ctas, batch)) {
+  if (use_tc(e, PDM_U8, PDM_U8, ctas, batch, pl.mode == 1)) {
     // the whole pass is one launch: the kernel's producer warps gather every step's rows themselves
     pdm_net_tc_args t;
     memset(&t, 0, sizeof(t));

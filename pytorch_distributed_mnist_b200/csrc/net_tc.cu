@@ -566,26 +566,33 @@ __device__ __forceinline__ void ll_exchange(const TcArgs& a, uint8_t* smem, uint
     const float2 v = gbuf[u];
     ll_store2(a.peers.inbox[p] + ((par + me) * kCtas + cta) * kLLSlot + (size_t)u * 2, v.x, v.y, seq);
   }
-  // poll: up to four units in flight per thread and round
-  for (int idx0 = t; idx0 < total; idx0 += 4 * kEpiThreads) {
+  // poll: up to eight units in flight per thread and round (one L2 round trip per round)
+  constexpr int kInFlight = 8;
+  for (int idx0 = t; idx0 < total; idx0 += kInFlight * kEpiThreads) {
     uint32_t pending = 0;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) if (idx0 + j * kEpiThreads < total) pending |= 1u << j;
+    for (int j = 0; j < kInFlight; ++j) if (idx0 + j * kEpiThreads < total) pending |= 1u << j;
     uint32_t spins = 0;
     uint64_t t0 = 0;
     while (pending != 0u) {
+      float x[kInFlight], y[kInFlight];
+      uint32_t got = 0;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
+      for (int j = 0; j < kInFlight; ++j) {                   // all loads first ...
         if (!((pending >> j) & 1u)) continue;
         const int idx = idx0 + j * kEpiThreads;
         const int k = idx / kLLUnits, u = idx - k * kLLUnits;
         const int p = k + (k >= me ? 1 : 0);
-        float x, y;
-        if (ll_load2(a.peers.inbox[me] + ((par + p) * kCtas + cta) * kLLSlot + (size_t)u * 2, seq, x, y)) {
-          rbuf[k * kLLUnits + u] = make_float2(x, y);
-          pending &= ~(1u << j);
-        }
+        if (ll_load2(a.peers.inbox[me] + ((par + p) * kCtas + cta) * kLLSlot + (size_t)u * 2, seq, x[j], y[j])) got |= 1u << j;
       }
+#pragma unroll
+      for (int j = 0; j < kInFlight; ++j) {                   // ... then the stores
+        if (!((got >> j) & 1u)) continue;
+        const int idx = idx0 + j * kEpiThreads;
+        const int k = idx / kLLUnits, u = idx - k * kLLUnits;
+        rbuf[k * kLLUnits + u] = make_float2(x[j], y[j]);
+      }
+      pending &= ~got;
       if (pending != 0u && (++spins & 1023u) == 0u && a.peers.timeout_ns != 0) {
         const uint64_t now = globaltimer_ns();
         if (t0 == 0) t0 = now;
