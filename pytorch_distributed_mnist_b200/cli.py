@@ -60,6 +60,10 @@ def build_parser():
     parser.add_argument('--arch', choices=('linear', 'cnn'), default='linear',
                         help='linear = the reference Net; cnn = the BASELINE.json MNIST CNN extension')
     parser.add_argument('--width', type=int, default=1, help='channel/width multiplier of --arch cnn')
+    parser.add_argument('--precision', choices=('tf32', 'fp32x3'), default='tf32',
+                        help='GEMM-shaped CNN layers: one tf32 tensor-core pass (default) or 3xTF32, which is '
+                             'fp32-faithful at three times the tensor-core work (SURVEY 7.6); the reference Net is '
+                             'fp32-faithful either way')
     parser.add_argument('--synthetic', action='store_true',
                         help='force the fixed-seed synthetic MNIST-shaped dataset (default: use idx files '
                              'under --root when present, synthetic otherwise)')

@@ -87,6 +87,9 @@ def _run(args):
         from .parallel import topology
         print(topology.discover().summary(range(args.world_size) if device.type == 'cuda' else None))
 
+    if getattr(args, 'precision', 'tf32') != 'tf32':
+        from .ops import gemm as _gemm
+        _gemm.set_precision(args.precision)
     model = build_model(getattr(args, 'arch', 'linear'), getattr(args, 'width', 1))
     if distributed_is_initialized():
         model.to(device)

@@ -134,6 +134,9 @@ class Trainer(object):
         world = getattr(self.model, 'world', 1)
         if world > 1 and not getattr(self.model, 'uses_peer', False):
             return False
+        from .ops import gemm
+        if gemm.get_precision() != 'tf32':
+            return False           # the native step executor issues single-pass tf32 GEMMs; 3xTF32 goes through autograd
         return cnn_ops.available()
 
     def _batches(self, loader):

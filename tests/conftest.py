@@ -25,6 +25,18 @@ def pytest_collection_modifyitems(config, items):
             item.add_marker(pytest.mark.skip(reason='needs >= 2 CUDA devices'))
 
 
+@pytest.fixture(autouse=True)
+def fp32_oracles():
+    """Every stock-PyTorch result a test compares against is computed in true fp32: cuDNN convolutions
+    default to TF32 (matmul does not), which would make a tf32 kernel look exact against a tf32 oracle."""
+    import torch
+    prev = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = prev
+
+
 @pytest.fixture(scope='session')
 def reference_module():
     """The reference's own module, imported read-only as the oracle."""

@@ -178,7 +178,8 @@ def test_cnn_module_matches_stock_ops_end_to_end():
     for (n, p), (_, q) in zip(model.named_parameters(), ref.named_parameters()):
         # norm-wise: single elements can differ by a flipped ReLU/max-pool decision at tf32 precision
         rel = ((p.grad - q.grad).norm() / (q.grad.norm() + 1e-12)).item()
-        assert rel < 5e-2, '{}: relative gradient error {}'.format(n, rel)
+        # measured against the true-fp32 oracle: <= 2.2e-2 (conv1.weight, at the end of the tf32 dgrad chain)
+        assert rel < 3e-2, '{}: relative gradient error {}'.format(n, rel)
 
 
 def test_cnn_trains_on_synthetic_data():
@@ -263,3 +264,60 @@ def test_trainer_uses_native_cnn_engine(free_port):
         model.close()
     finally:
         dist.destroy_process_group()
+
+
+def _train_cnn(model, opt, x, y, steps, batch, ours):
+    losses = []
+    for i in range(steps):
+        s = (i * batch) % (x.size(0) - batch + 1)
+        logits = model(x[s:s + batch])
+        loss = F.cross_entropy(logits, y[s:s + batch])
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+    return losses
+
+
+@pytest.mark.parametrize('precision', ['tf32', 'fp32x3'])
+def test_accuracy_gate_against_fp32_stock(precision, capsys):
+    """the CNN trained on our kernels and on stock fp32 PyTorch ops (TF32 off) from the same
+    initialisation and data order (dropout off, so both see the same function): final loss within tolerance,
+    top-1 on the fixed synthetic test set equal to within a handful of borderline images."""
+    import pytorch_distributed_mnist_b200 as pdm
+    from pytorch_distributed_mnist_b200.data import mnist
+    from pytorch_distributed_mnist_b200.ops import cnn_ops, gemm
+    images, labels = mnist.synthetic_mnist(True, size=8192)
+    timg, tlab = mnist.synthetic_mnist(False, size=2048)
+    x = torch.from_numpy(images).cuda().view(-1, 784).float().div(255).sub(0.1307).div(0.3081)
+    y = torch.from_numpy(labels).cuda().long()
+    tx = torch.from_numpy(timg).cuda().view(-1, 784).float().div(255).sub(0.1307).div(0.3081)
+    ty = torch.from_numpy(tlab).cuda().long()
+    torch.manual_seed(21)
+    ours = pdm.CNN(p1=0.0, p2=0.0).cuda().train()
+    stock = pdm.CNN(p1=0.0, p2=0.0).cuda().train()
+    stock.load_state_dict(ours.state_dict())
+    prev = gemm.set_precision(precision)
+    try:
+        lo = _train_cnn(ours, pdm.FusedAdam(ours.parameters(), lr=1e-3), x, y, 192, 128, True)
+        with torch.no_grad():
+            acc_o = (ours.eval()(tx).argmax(1) == ty).float().mean().item()
+    finally:
+        gemm.set_precision(prev)
+    saved = cnn_ops.available
+    cnn_ops.available = lambda: False                       # the same module on stock ops, true fp32
+    try:
+        ls = _train_cnn(stock, torch.optim.Adam(stock.parameters(), lr=1e-3), x, y, 192, 128, False)
+        with torch.no_grad():
+            acc_s = (stock.eval()(tx).argmax(1) == ty).float().mean().item()
+    finally:
+        cnn_ops.available = saved
+    with capsys.disabled():
+        print('\n[accuracy gate, {}] final loss ours {:.5f} vs fp32 stock {:.5f}; top-1 on 2048 fixed test images '
+              '{:.4f} vs {:.4f}'.format(precision, sum(lo[-8:]) / 8, sum(ls[-8:]) / 8, acc_o, acc_s))
+    assert acc_s > 0.9
+    # measured: 2 (tf32) and 3 (fp32x3) of 2048 images differ -- borderline images flip with any change of
+    # summation order (FMA kernels, fused Adam), in either direction, whatever the GEMM precision
+    assert abs(acc_o - acc_s) <= 6 / 2048 + 1e-9
+    tol = 0.05 if precision == 'tf32' else 0.02
+    assert abs(sum(lo[-8:]) - sum(ls[-8:])) / 8 <= tol * max(sum(ls[-8:]) / 8, 0.05)

@@ -82,3 +82,64 @@ def test_conv3x3_forward_dgrad_wgrad(batch, cin, cout):
                 M=cout, N=9 * cin, K=batch * H * W, splits=4)
     ref_dw = w.grad.permute(0, 2, 3, 1).reshape(cout, 9 * cin)
     _close(dw, ref_dw, batch * 576)
+
+
+def _errs(fn_ours, fn_stock_tf32, ref64):
+    scale = ref64.abs().max().item()
+    return ((fn_ours().double() - ref64).abs().max().item() / scale,
+            (fn_stock_tf32().double() - ref64).abs().max().item() / scale)
+
+
+def test_measured_error_against_fp64_next_to_stock_tf32(capsys):
+    """The number the accuracy discussion needs: max error of our tf32 GEMM and conv against an
+    fp64 evaluation, next to stock cuBLAS / cuDNN with TF32 allowed on the same inputs -- same precision class --
+    and the 3xTF32 mode, which must be fp32-faithful."""
+    from pytorch_distributed_mnist_b200.ops import gemm as G
+    torch.manual_seed(5)
+    A, B = torch.randn(512, 2304, device='cuda'), torch.randn(256, 2304, device='cuda')
+    ref = A.double() @ B.double().t()
+
+    def stock():
+        torch.backends.cuda.matmul.allow_tf32 = True
+        try:
+            return A @ B.t()
+        finally:
+            torch.backends.cuda.matmul.allow_tf32 = False
+
+    ours, stock_err = _errs(lambda: G.gemm(A, B), stock, ref)
+    x3 = (G.gemm(A, B, precision='fp32x3').double() - ref).abs().max().item() / ref.abs().max().item()
+    fp32 = ((A @ B.t()).double() - ref).abs().max().item() / ref.abs().max().item()
+    with capsys.disabled():
+        print('\n[gemm 512x256x2304] max err / max|ref|: ours tf32 {:.2e}, cuBLAS tf32 {:.2e}, ours fp32x3 {:.2e}, '
+              'cuBLAS fp32 {:.2e}'.format(ours, stock_err, x3, fp32))
+    # same precision class as the library's tf32; the tensor core TRUNCATES fp32 operands to tf32 where cuBLAS
+    # rounds them to nearest first, which costs a factor of two to three in max error (measured: 6.9e-4 vs 2.5e-4)
+    assert ours <= 4.0 * stock_err + 1e-6
+    assert x3 <= 4.0 * fp32 + 2e-7                 # 3xTF32 is fp32-faithful
+    # 3x3 convolution (conv2 shape), forward
+    x = torch.randn(4, 32, 26, 26, device='cuda')
+    w = torch.randn(64, 32, 3, 3, device='cuda') * 0.1
+    ref = F.conv2d(x.double(), w.double())
+    x2d = x.permute(0, 2, 3, 1).reshape(4 * 676, 32).contiguous()
+    wk = w.permute(0, 2, 3, 1).reshape(64, 288).contiguous()
+
+    def ours_conv(precision):
+        out = G.gemm(x2d, wk, mode=G.MODE_CONV, img_w=26, cblocks=1, shift_sign=1, M=4 * 676, N=64, K=288,
+                     precision=precision)
+        return out.view(4, 26, 26, 64)[:, :24, :24, :].permute(0, 3, 1, 2)
+
+    def stock_conv():
+        torch.backends.cudnn.allow_tf32 = True
+        try:
+            return F.conv2d(x, w)
+        finally:
+            torch.backends.cudnn.allow_tf32 = False
+
+    ours, stock_err = _errs(lambda: ours_conv('tf32'), stock_conv, ref)
+    x3 = (ours_conv('fp32x3').double() - ref).abs().max().item() / ref.abs().max().item()
+    fp32 = (F.conv2d(x, w).double() - ref).abs().max().item() / ref.abs().max().item()
+    with capsys.disabled():
+        print('[conv 32->64 3x3]   max err / max|ref|: ours tf32 {:.2e}, cuDNN tf32 {:.2e}, ours fp32x3 {:.2e}, '
+              'cuDNN fp32 {:.2e}'.format(ours, stock_err, x3, fp32))
+    assert ours <= 4.0 * stock_err + 1e-6
+    assert x3 <= 4.0 * fp32 + 2e-7
