@@ -10,8 +10,8 @@ What the stock wrapper does natively in C++ and what replaces it:
 =====================================  =======================================
 stock (c10d Reducer)                   here
 =====================================  =======================================
-``_verify_params_across_processes``    shape digest compared through the store /
-(K14)                                  an all-gather of one int64 per rank
+``_verify_params_across_processes``    shape digest published and compared through
+(K14)                                  the rendezvous store (no collective)
 ``_broadcast_coalesced`` from rank 0   one peer-memory pull of the flat
 (K15)                                  parameter buffer (``pdm_comm_broadcast``)
 ``_compute_bucket_assignment_by_size`` ``assign_buckets``: reverse parameter
@@ -34,6 +34,7 @@ flat update afterwards (``GroupComm``).
 from __future__ import annotations
 
 import hashlib
+import itertools
 from collections import OrderedDict
 
 import torch
@@ -101,6 +102,16 @@ def _shape_digest(params):
     return int.from_bytes(h.digest()[:7], 'big')
 
 
+_instances = itertools.count()
+
+
+def _store_allgather(store, tag, rank, world, value):
+    """Every rank publishes ``value`` (bytes) under ``tag`` in the rendezvous store and reads everyone's:
+    the construction-time metadata exchanges (K14, peer-capability flags) need no collective and no GPU."""
+    store.set('{}/{}'.format(tag, rank), value)
+    return [bytes(store.get('{}/{}'.format(tag, r))) for r in range(world)]
+
+
 class DistributedDataParallel(nn.Module):
 
     def __init__(self, module, device_ids=None, output_device=None, broadcast_buffers=True,
@@ -129,13 +140,28 @@ class DistributedDataParallel(nn.Module):
         self.broadcast_buffers = broadcast_buffers
         self._process_group = process_group
 
+        # construction-time metadata travels through the rendezvous store (the native one when given)
+        self._tag = 'pdm/ddp{}'.format(next(_instances))
+        self._meta_store = None
+        if self.world > 1:
+            if store is not None:
+                self._meta_store = store
+            elif process_group is None:
+                from .peer import default_store
+                try:
+                    self._meta_store = default_store()
+                except Exception:  # noqa: BLE001 - no default store (exotic init): fall back to collectives
+                    self._meta_store = None
         # -- communicator ---------------------------------------------------
         numel = sum((p.numel() + 3) // 4 * 4 for p in params)
         section = (numel + 63) // 64 * 64
         self.comm = None
         if self.device.type == 'cuda' and comm in ('auto', 'peer'):
             ok = PeerComm.supported(self.world) if self.world > 1 else True
-            if self.world > 1:
+            if self.world > 1 and self._meta_store is not None:
+                flags = _store_allgather(self._meta_store, self._tag + '/peer_ok', self.rank, self.world, b'1' if ok else b'0')
+                ok = all(f == b'1' for f in flags)
+            elif self.world > 1:
                 flags = [None] * self.world
                 dist.all_gather_object(flags, bool(ok), group=process_group)
                 ok = all(flags)
@@ -203,6 +229,14 @@ class DistributedDataParallel(nn.Module):
         if self.world == 1:
             return
         mine = _shape_digest(params)
+        if self._meta_store is not None:
+            # K14 through the store: no collective, no device work
+            got = [int(v.decode()) for v in _store_allgather(self._meta_store, self._tag + '/digest', self.rank, self.world,
+                                                             str(mine).encode())]
+            if any(g != got[0] for g in got):
+                raise RuntimeError('DistributedDataParallel: parameter shapes differ across ranks '
+                                   '(digests {}); every rank must build the same model'.format(got))
+            return
         t = torch.tensor([mine], dtype=torch.int64, device=self.device if dist.get_backend(group) == 'nccl' else 'cpu')
         out = [torch.zeros_like(t) for _ in range(self.world)]
         dist.all_gather(out, t, group=group)

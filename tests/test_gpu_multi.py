@@ -147,10 +147,12 @@ def _assert_close_after_adam(a, b, lr, steps):
     visible fraction of lr for a handful of elements.  Compare the bulk tightly and bound the outliers:
     measured on B200, 4 steps: mean drift ~1e-7, 4 of 1.18 M elements above 2e-4 (max 3.8e-4) at 8 GPUs."""
     d = (a.detach() - b.detach()).abs()
-    assert d.max().item() <= 0.5 * lr * steps, 'max drift {:.3e}'.format(d.max().item())
-    assert d.mean().item() < 5e-6, 'mean drift {:.3e}'.format(d.mean().item())
+    # bounds a few times what was measured (passes at 2 and 8 GPUs: profiles/raw/r2/): a reducer or slicing
+    # bug that touches even a hundred elements fails here
+    assert d.max().item() <= 1e-3, 'max drift {:.3e}'.format(d.max().item())
+    assert d.mean().item() < 2e-6, 'mean drift {:.3e}'.format(d.mean().item())
     outliers = int((d > 2e-4 + 2e-3 * b.detach().abs()).sum().item())
-    assert outliers <= d.numel() // 200, '{} of {} elements drifted'.format(outliers, d.numel())
+    assert outliers <= 64, '{} of {} elements drifted'.format(outliers, d.numel())
 
 
 def _tc_worker(rank, world, port):
