@@ -8,8 +8,8 @@ bandwidth -- but it still has to know three things before it maps anybody's memo
 * can every pair of GPUs in the job load/store each other's memory (else: ``--comm group``),
 * is the path NVLink (and through a switch) or PCIe, which decides whether the one-shot or the
   two-shot all-reduce wins for a given bucket size (``plan_allreduce``),
-* do the devices support multicast objects (NVLS), recorded for the report; the multimem path
-  itself is not implemented in this round.
+* do the devices support multicast objects (NVLS): the reducer then reduces large models in the
+  switch (``parallel/nvls.py``, ``parallel/ddp.py``: >= 8 MB at >= 4 GPUs).
 
 Sources: the CUDA runtime through torch (peer access), NVML (per-link state, remote device type,
 P2P capability matrix) and the driver attribute for multicast.  Every source is optional: a probe
