@@ -102,6 +102,8 @@ struct Misc {                     // lives at kOffMisc
 };
 static_assert(sizeof(Misc) <= kMiscBytes, "Misc outgrew its slot");
 
+constexpr int kInlineSteps = 96;       // launches of up to this many steps need no constant upload
+
 struct TcArgs {
   const uint8_t* x;
   const uint8_t* y;
@@ -124,6 +126,7 @@ struct TcArgs {
   uint8_t* ring;                  // optional device ring of kRingSlots blocks (rows + labels): the feeder cluster fills it
   uint32_t* ring_flags;           // [2][kRingSlots]: blocks made ready (x13 per fill) / consumed (x13 per use)
   const float2* adam;             // per step of this launch: {lr / (1 - beta1^t), 1 / sqrt(1 - beta2^t)} (host-computed, double precision)
+  float2 adam_inline[kInlineSteps];   // the same for short launches, carried in the kernel parameters (adam == nullptr)
   float inv_world;
   uint32_t skew_ns;               // fault injection: random pause (< skew_ns) before this rank publishes its gradient
   int dbg;                        // bring-up switches (PDM_TC_DBG bit mask); 0 in production
@@ -137,7 +140,7 @@ __device__ __forceinline__ long long clock_now() {
   return c;
 }
 // stamps go to shared memory (a global store per stamp perturbs what it measures) and are dumped at the end
-#define TC_TRACE(cond, step, slot) do { if (a.trace != nullptr && (cond) && (step) < kTraceSteps) \
+#define TC_TRACE(cond, step, slot) do { if (kTrace && (cond) && (step) < kTraceSteps) \
     reinterpret_cast<long long*>(smem + kOffTrace)[(step) * 32 + (slot)] = clock_now(); } while (0)
 
 // ---------------------------------------------------------------------------- PTX wrappers
@@ -355,6 +358,7 @@ __device__ __forceinline__ void px4_to_bf16(uint32_t w, uint32_t& lo, uint32_t& 
 // 224 threads stream the rows (and labels) of the next block into registers while the current block
 // computes, then (once the wgrad MMAs of the current block have finished reading the tile) convert
 // them to bf16 and store them as 8x8 core matrices.
+template <bool kTrace>
 __device__ __forceinline__ void producer_loop(const TcArgs& a, uint8_t* smem, Misc* ms, int pt, int cta) {
   const int col0 = cta * kCols;
   const int valid_cols = min(kCols, kIn - col0);
@@ -495,6 +499,7 @@ __device__ __forceinline__ void feeder_loop(const TcArgs& a, int tid, int cta) {
 }
 
 // ---------------------------------------------------------------------------- MMA warp (one lane)
+template <bool kTrace>
 __device__ __forceinline__ void mma_loop(const TcArgs& a, uint8_t* smem, Misc* ms, uint32_t tmem_base) {
   const uint32_t tile = smem_u32(smem + kOffTile), dlop = smem_u32(smem + kOffDlop), wop = smem_u32(smem + kOffWop);
   uint32_t it = 0;
@@ -566,8 +571,8 @@ __device__ __forceinline__ void ll_exchange(const TcArgs& a, uint8_t* smem, uint
     const float2 v = gbuf[u];
     ll_store2(a.peers.inbox[p] + ((par + me) * kCtas + cta) * kLLSlot + (size_t)u * 2, v.x, v.y, seq);
   }
-  // poll: up to eight units in flight per thread and round (one L2 round trip per round)
-  constexpr int kInFlight = 8;
+  // poll: up to four units in flight per thread and round (eight spill registers into the hot loop) (one L2 round trip per round)
+  constexpr int kInFlight = 4;
   for (int idx0 = t; idx0 < total; idx0 += kInFlight * kEpiThreads) {
     uint32_t pending = 0;
 #pragma unroll
@@ -666,6 +671,7 @@ __device__ __forceinline__ void publish_weights(uint8_t* smem, Misc* ms, int t, 
 }
 
 // ---------------------------------------------------------------------------- epilogue / optimizer warps
+template <bool kTrace>
 __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Misc* ms, uint32_t tmem_base, int t, int cta) {
   const int warp = t >> 5, lane = t & 31;
   const int col = cta * kCols + t;                       // input column of thread t < 64
@@ -710,7 +716,7 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
     mbar_arrive(&ms->bar_wop);
     epi_sync();
     TC_TRACE(t == 0, step, 13);
-    const float2 adam_c = __ldg(a.adam + step);           // consumed at the end of the step: the latency is hidden
+    const float2 adam_c = a.adam != nullptr ? __ldg(a.adam + step) : a.adam_inline[step];   // consumed at the end of the step
     float wsumn[kOut];
 #pragma unroll
     for (int n = 0; n < kOut; ++n) wsumn[n] = kShift * (ms->wsum[0][n] + ms->wsum[1][n]);
@@ -919,6 +925,7 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
 }
 
 // ---------------------------------------------------------------------------- the kernel
+template <bool kTrace>
 __global__ void __launch_bounds__(kThreads, 1) net_tc_kernel(const __grid_constant__ TcArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   Misc* ms = reinterpret_cast<Misc*>(smem + kOffMisc);
@@ -930,8 +937,12 @@ __global__ void __launch_bounds__(kThreads, 1) net_tc_kernel(const __grid_consta
     feeder_loop(a, tid, (int)cta);
     return;
   }
-  // zero every operand buffer (padding rows / columns must hold finite values), then the ones column
-  for (uint32_t i = tid; i < kSmemBytes / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0u, 0u, 0u, 0u);
+  // Nothing but the bookkeeping block (and the trace area) needs defined contents: every operand element that
+  // reaches an accumulator row / column the epilogues read is written before it is used; padding (operand rows
+  // 10-15, tile column blocks 9-15, the other seven entries of the ones block) only feeds accumulator rows and
+  // columns nobody reads, so whatever bits they hold (NaN included) are harmless.  The ones column is set once.
+  for (uint32_t i = tid; i < (kSmemBytes - kOffMisc) / 16; i += kThreads)
+    reinterpret_cast<uint4*>(smem + kOffMisc)[i] = make_uint4(0u, 0u, 0u, 0u);
   __syncthreads();
   for (int r = tid; r < kBlkRows; r += kThreads)
     *reinterpret_cast<uint16_t*>(smem + kOffTile + (uint32_t)(r >> 3) * kSr + 8u * kSc + (uint32_t)(r & 7) * 16u) = 0x3F80;  // bf16 1.0
@@ -955,17 +966,17 @@ __global__ void __launch_bounds__(kThreads, 1) net_tc_kernel(const __grid_consta
   const uint32_t tmem_base = ms->tmem_slot;
 
   if (tid >= kEpiFirst) {
-    epilogue_loop(a, smem, ms, tmem_base, tid - kEpiFirst, (int)cta);
+    epilogue_loop<kTrace>(a, smem, ms, tmem_base, tid - kEpiFirst, (int)cta);
   } else if (warp == kMmaWarp) {
-    if ((tid & 31) == 0) mma_loop(a, smem, ms, tmem_base);
+    if ((tid & 31) == 0) mma_loop<kTrace>(a, smem, ms, tmem_base);
     __syncwarp();
   } else {
-    producer_loop(a, smem, ms, tid, (int)cta);
+    producer_loop<kTrace>(a, smem, ms, tid, (int)cta);
   }
 
   tc_fence_before();
   __syncthreads();
-  if (a.trace != nullptr)
+  if (kTrace && a.trace != nullptr)
     for (int i = tid; i < kTraceSteps * 32; i += kThreads)
       a.trace[(size_t)cta * kTraceSteps * 32 + i] = reinterpret_cast<const long long*>(smem + kOffTrace)[i];
   cluster_sync_all();                     // no CTA leaves while a peer may still address its shared memory
@@ -1008,13 +1019,15 @@ extern "C" int pdm_net_tc_supported(int device) {
     cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
     cudaDeviceGetAttribute(&cluster, cudaDevAttrClusterLaunch, device);
     if (major == 10 && cluster) {
-      if (cudaFuncSetAttribute(net_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes) == cudaSuccess &&
-          cudaFuncSetAttribute(net_tc_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
+      if (cudaFuncSetAttribute(net_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes) == cudaSuccess &&
+          cudaFuncSetAttribute(net_tc_kernel<false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess &&
+          cudaFuncSetAttribute(net_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes) == cudaSuccess &&
+          cudaFuncSetAttribute(net_tc_kernel<true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
         cudaLaunchConfig_t cfg;
         cudaLaunchAttribute attr[1];
         tc_launch_config(&cfg, attr, nullptr);
         int nclusters = 0;
-        if (cudaOccupancyMaxActiveClusters(&nclusters, net_tc_kernel, &cfg) == cudaSuccess && nclusters >= 1) ok = 1;
+        if (cudaOccupancyMaxActiveClusters(&nclusters, net_tc_kernel<false>, &cfg) == cudaSuccess && nclusters >= 1) ok = 1;
       }
     }
     cudaGetLastError();
@@ -1145,22 +1158,28 @@ extern "C" int pdm_net_tc_run(const pdm_net_tc_args* g, pdm_stream_t stream) {
     a.peers = g->peers;
     a.peers.world = world;
     a.peers.seq = g->peers.seq + (uint32_t)done;
+    float2* consts = n <= kInlineSteps ? a.adam_inline : adam_host;
     for (long long i = 0; i < n; ++i) {
       const long long idx = a.step0 + i;
       const double sidx = (double)(idx < 1 ? 1 : idx);
-      adam_host[i] = make_float2(0.f, 1.f);
+      consts[i] = make_float2(0.f, 1.f);
       if (h.opt == PDM_OPT_ADAM) {
-        adam_host[i].x = (float)((double)h.lr / (1.0 - pow((double)h.beta1, sidx)));
-        adam_host[i].y = (float)(1.0 / sqrt(1.0 - pow((double)h.beta2, sidx)));
+        consts[i].x = (float)((double)h.lr / (1.0 - pow((double)h.beta1, sidx)));
+        consts[i].y = (float)(1.0 / sqrt(1.0 - pow((double)h.beta2, sidx)));
       }
     }
-    // pageable source: the runtime stages it before returning, so adam_host may be reused at once
-    PDM_CHECK_CUDA(cudaMemcpyAsync(adam_dev, adam_host, (size_t)n * sizeof(float2), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    if (n <= kInlineSteps) {
+      a.adam = nullptr;              // short launch: the constants travel in the kernel parameters
+    } else {
+      // pageable source: the runtime stages it before returning, so adam_host may be reused at once
+      PDM_CHECK_CUDA(cudaMemcpyAsync(adam_dev, adam_host, (size_t)n * sizeof(float2), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    }
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
     tc_launch_config(&cfg, attr, (cudaStream_t)stream, a.ring != nullptr ? 2 : 1);
     void* params[] = {&a};
-    PDM_CHECK_CUDA(cudaLaunchKernelExC(&cfg, (const void*)net_tc_kernel, params));
+    const void* fn = a.trace != nullptr ? (const void*)net_tc_kernel<true> : (const void*)net_tc_kernel<false>;
+    PDM_CHECK_CUDA(cudaLaunchKernelExC(&cfg, fn, params));
   }
   return PDM_OK;
 }
