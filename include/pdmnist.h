@@ -393,6 +393,37 @@ int pdm_comm_allreduce_optim(pdm_comm* c, size_t grad_off, size_t out_off, size_
 int pdm_comm_destroy(pdm_comm* c);
 
 /* ------------------------------------------------------------------------
+ * Gradient reducer for arbitrary models (reducer.cu; the role of c10d's Reducer).
+ * Gradients are slices of a flat buffer inside the communicator's (or NVLS region's) data area;
+ * a bucket is a 4-float-aligned range of it.  pdm_reducer_mark_ready is called from autograd's
+ * post-accumulate hook; when a bucket's last gradient has landed -- and every earlier bucket has
+ * been launched -- the reducer orders the communication stream after the compute stream and
+ * launches ONE fused all-reduce + 1/W + optimizer kernel over the range (hyper->opt NONE / NULL:
+ * the averaged gradient in place), and after the last bucket hands the compute stream the result.
+ * comm == nvls == NULL: bookkeeping only; the caller reduces the buckets reported in first/count.
+ * ---------------------------------------------------------------------- */
+struct pdm_nvls;
+typedef struct pdm_reducer pdm_reducer;
+typedef struct pdm_reducer_config {
+  int32_t n_params, n_buckets;
+  const int32_t* bucket_of;        /* [n_params] */
+  const int64_t* bucket_lo;        /* [n_buckets] float offsets into the flat buffers */
+  const int64_t* bucket_hi;
+  size_t grads_off, params_off, m_off, v_off;   /* byte offsets of the flat buffers in the data area */
+  pdm_comm* comm;                  /* peer-memory communicator, or NULL */
+  struct pdm_nvls* nvls;           /* NVLS region (takes precedence), or NULL */
+  int32_t world;
+  int32_t device;                  /* CUDA device of the streams; -1 without native communication */
+} pdm_reducer_config;
+int pdm_reducer_create(pdm_reducer** out, const pdm_reducer_config* cfg);
+int pdm_reducer_arm(pdm_reducer* r);   /* start of a training forward; PDM_ERR_STATE if the last pass is unfinished */
+int pdm_reducer_mark_ready(pdm_reducer* r, int32_t param, const pdm_hyper* hyper, pdm_stream_t compute,
+                           pdm_stream_t comm_stream, int32_t* first, int32_t* count);
+int pdm_reducer_state(pdm_reducer* r, int32_t* next, int64_t* launches, int32_t* pending, int32_t* order,
+                      int32_t* n_order);
+int pdm_reducer_destroy(pdm_reducer* r);
+
+/* ------------------------------------------------------------------------
  * NVLS (multicast / multimem) region (nvls.cu): the in-switch path NCCL takes for large
  * all-reduces.  The reducer uses it for models of >= 8 MB at 4 or more GPUs
  * (parallel/ddp.py; PDM_NVLS=0 / 1 forces it off / on); it moves 1 + 1/W of the payload per GPU

@@ -213,11 +213,21 @@ class DistributedDataParallel(nn.Module):
         for b, bk in enumerate(self.buckets):
             for i in bk['params']:
                 self._bucket_of[i] = b
-        self._pending = [len(bk['params']) for bk in self.buckets]
-        self._ready = [False] * len(self.buckets)
-        self._next_launch = 0
         self._works = []
         self.comm_stream = torch.cuda.Stream(device=self.device) if self.device.type == 'cuda' else None
+        # the native reducer (csrc/reducer.cu) counts readiness, orders the streams and launches the
+        # fused bucket kernels; without a native communicator it reports the buckets to reduce here
+        from .reducer import NativeReducer
+        region = self.nvls if self.nvls is not None else (self.comm if self.uses_peer else None)
+        self._reducer = NativeReducer(
+            [self._bucket_of[i] for i in range(len(params))], [(bk['lo'], bk['hi']) for bk in self.buckets],
+            world=self.world,
+            comm_handle=self.comm.handle if (self.uses_peer and self.nvls is None) else None,
+            nvls_handle=self.nvls.handle if self.nvls is not None else None,
+            offsets=[region.offset_of(getattr(self.flat, n)) for n in ('grads', 'params', 'exp_avg', 'exp_avg_sq')]
+            if region is not None else None,
+            device=(self.device.index or 0) if region is not None else -1)
+        self._hyper = None
         self.require_backward_grad_sync = True
         self._hooks = []
         for i, p in enumerate(params):
@@ -277,19 +287,17 @@ class DistributedDataParallel(nn.Module):
         # Stock DDP refuses to start an iteration when the previous one did not finish its reduction
         # ("Expected to have finished reduction in the prior iteration"): a parameter that received no
         # gradient leaves its bucket -- and every later one -- unreduced, and the ranks drift apart.
-        started = any(p != len(bk['params']) for p, bk in zip(self._pending, self.buckets))
-        if started and self._next_launch < len(self.buckets):
-            missing = [i for b in range(self._next_launch, len(self.buckets)) for i in self.buckets[b]['params']
-                       if self._pending[b] > 0]
+        if not self._reducer.arm():
+            st = self._reducer.state()
+            missing = [i for b in range(st['next'], len(self.buckets)) for i in self.buckets[b]['params']
+                       if st['pending'][b] > 0]
             raise RuntimeError(
                 'DistributedDataParallel: the previous backward pass did not produce gradients for every parameter '
                 '(buckets {}..{} were never reduced; parameters without a gradient are among indices {}). Every '
                 'parameter must take part in the loss (there is no find_unused_parameters mode), or wrap the '
                 'extra forward passes in no_sync() / torch.no_grad().'.format(
-                    self._next_launch, len(self.buckets) - 1, missing[:8]))
-        self._pending = [len(bk['params']) for bk in self.buckets]
-        self._ready = [False] * len(self.buckets)
-        self._next_launch = 0
+                    st['next'], len(self.buckets) - 1, missing[:8]))
+        self._hyper = None
         self.flat.attach_grads()
 
     class _NoSync(object):
@@ -317,55 +325,40 @@ class DistributedDataParallel(nn.Module):
                 # autograd installed its own tensor (grad was None): move it into the bucket
                 flat.view_of('grads', index).copy_(param.grad)
                 param.grad = flat.view_of('grads', index)
-            b = self._bucket_of[index]
-            self._pending[b] -= 1
-            if self._pending[b] == 0:
-                self._ready[b] = True
-                while self._next_launch < len(self.buckets) and self._ready[self._next_launch]:
-                    self._launch_bucket(self._next_launch)
-                    self._next_launch += 1
+            if self.uses_peer:
+                if self._hyper is None and self.fuse_optimizer and flat.optimizer is not None:
+                    self._hyper = flat.optimizer.hyper(flat.optimizer.step_count + 1)
+                first, count = self._reducer.mark_ready(
+                    index, self._hyper, torch.cuda.current_stream(self.device).cuda_stream, self.comm_stream.cuda_stream)
+            else:
+                first, count = self._reducer.mark_ready(index)
+            for b in range(first, first + count):
+                self._after_launch(b) if self.uses_peer else self._reduce_with_group(b)
         return hook
 
-    def _launch_bucket(self, b):
+    def _after_launch(self, b):
+        """Bookkeeping for a bucket the native reducer launched on the communication stream."""
         bk = self.buckets[b]
-        lo, hi = bk['lo'], bk['hi']
-        flat = self.flat
         self.stats['bucket_launches'] += 1
-        if self.uses_peer:
-            opt = flat.optimizer if self.fuse_optimizer else None
-            cs = self.comm_stream
-            cs.wait_stream(torch.cuda.current_stream(self.device))
-            with torch.cuda.stream(cs):
-                if opt is not None and self.nvls is not None:
-                    h = opt.hyper(opt.step_count + 1)
-                    flat.mark_sharded(lo, hi, self.world, force=True)      # rank r updates slice r of every bucket
-                    self.nvls.allreduce_optim(flat.grads[lo:hi], flat.params[lo:hi], flat.exp_avg[lo:hi],
-                                              flat.exp_avg_sq[lo:hi], h, stream=cs)
-                elif opt is not None:
-                    h = opt.hyper(opt.step_count + 1)
-                    flat.mark_sharded(lo, hi, self.world)      # >= 256 KB: two-shot, state updated slice-wise
-                    self.comm.allreduce_optim(flat.grads[lo:hi], flat.params[lo:hi], flat.exp_avg[lo:hi],
-                                              flat.exp_avg_sq[lo:hi], h, stream=cs)
-                elif self.nvls is not None:
-                    self.nvls.allreduce(flat.grads[lo:hi], flat.grads[lo:hi], average=True, stream=cs)
-                elif self.world > 1:
-                    self.comm.allreduce(flat.grads[lo:hi], flat.grads[lo:hi], average=True, algo=2, stream=cs)
-            if opt is not None and b == len(self.buckets) - 1:
-                flat.fused_applied = True
+        if self._hyper is not None:
+            # slice-wise optimizer state: every bucket in the switch, buckets >= 256 KB through peer memory
+            self.flat.mark_sharded(bk['lo'], bk['hi'], self.world, force=self.nvls is not None)
             if b == len(self.buckets) - 1:
-                # the caller's stream continues only after the last bucket is applied
-                torch.cuda.current_stream(self.device).wait_stream(cs)
-        else:
-            if self.world > 1:
-                g = flat.grads[lo:hi]
-                g.div_(self.world)
-                work = self.comm.allreduce_async(g)
-                self._works.append(work)
-            if b == len(self.buckets) - 1:
-                for w in self._works:
-                    if w is not None:
-                        w.wait()
-                self._works = []
+                self.flat.fused_applied = True
+
+    def _reduce_with_group(self, b):
+        """No native communicator (gloo / GPUs without peer access): torch.distributed reduces the bucket."""
+        bk = self.buckets[b]
+        self.stats['bucket_launches'] += 1
+        if self.world > 1:
+            g = self.flat.grads[bk['lo']:bk['hi']]
+            g.div_(self.world)
+            self._works.append(self.comm.allreduce_async(g))
+        if b == len(self.buckets) - 1:
+            for w in self._works:
+                if w is not None:
+                    w.wait()
+            self._works = []
 
     # -- checkpoint surface ---------------------------------------------------------
     def state_dict(self, *args, **kwargs):
@@ -384,6 +377,9 @@ class DistributedDataParallel(nn.Module):
         for h in self._hooks:
             h.remove()
         self._hooks = []
+        if getattr(self, '_reducer', None) is not None:
+            self._reducer.close()
+            self._reducer = None
         if self.nvls is not None:
             self.nvls.close()
             self.nvls = None

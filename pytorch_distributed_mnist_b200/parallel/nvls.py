@@ -211,6 +211,10 @@ class NvlsRegion(object):
         self.allreduce_optim(src, dst, None, None, no_opt_hyper(), grad_scale=(1.0 / self.world) if average else 1.0,
                              stream=stream)
 
+    @property
+    def handle(self):
+        return self._h
+
     def check_status(self):
         st = ctypes.c_int(0)
         _lib.check(self._lib.pdm_nvls_status(self._h, ctypes.byref(st)), 'pdm_nvls_status')

@@ -276,3 +276,30 @@ def test_epoch_plan_is_built_at_set_sample_epoch():
     assert torch.equal(loader.epoch_indices(), want)          # asking twice in one epoch is fine
     loader.sampler.set_epoch(7)                                # epoch moved behind the loader's back
     assert torch.equal(loader.epoch_indices()[:500], loader.sampler.indices(7))
+
+
+def test_native_reducer_launches_buckets_in_index_order():
+    """bucket-ready counting and in-order launches live in csrc/reducer.cu.  A later bucket
+    that becomes ready first is held back until every earlier one has gone out."""
+    from pytorch_distributed_mnist_b200.parallel.reducer import NativeReducer
+    # 5 parameters; bucket 0 = {4, 3}, bucket 1 = {2}, bucket 2 = {1, 0} (reverse order, like assign_buckets)
+    r = NativeReducer([2, 2, 1, 0, 0], [(32, 48), (16, 32), (0, 16)])
+    assert r.arm()
+    assert r.mark_ready(2) == (0, 0)            # bucket 1 complete, bucket 0 still open: held
+    assert r.mark_ready(4) == (0, 0)
+    assert r.mark_ready(3) == (0, 2)            # bucket 0 closes: 0 and the held 1 go out together
+    assert r.mark_ready(0) == (2, 0)
+    st = r.state()
+    assert st['next'] == 2 and st['pending'] == [0, 0, 1] and st['order'] == [0, 1]
+    assert not r.arm()                          # unfinished reduction is refused, state kept
+    assert r.state()['pending'] == [0, 0, 1]
+    assert r.mark_ready(1) == (2, 1)
+    assert r.state()['launches'] == 3
+    with pytest.raises(RuntimeError, match='marked twice'):
+        r.mark_ready(1)
+    assert r.arm() and r.state()['order'] == []
+    r.close()
+    with pytest.raises(RuntimeError, match='4-float aligned'):
+        NativeReducer([0], [(0, 6)])
+    with pytest.raises(RuntimeError, match='maps to bucket'):
+        NativeReducer([1], [(0, 8)])

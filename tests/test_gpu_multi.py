@@ -261,6 +261,11 @@ def _cnn_worker(rank, world, port, native=False, nvls=False):
         for o in others:
             assert torch.equal(o, mine), 'replicas diverged in the bucketed fused path'
         assert o_opt.step_count == 4
+        if eng is None:
+            # the autograd path: csrc/reducer.cu launched every bucket kernel, in index order
+            st = ours._reducer.state()
+            assert ours._reducer.native_comm and st['launches'] == 4 * len(ours.buckets)
+            assert st['order'] == list(range(len(ours.buckets))) and st['next'] == len(ours.buckets)
         # the fc bucket (4.7 MB) takes the two-shot kernel: Adam's moments are updated slice-wise by their
         # owners and must be gathered before a checkpoint; afterwards every rank holds the same complete state
         assert ours.flat.state_stale and len(ours.flat.sharded) >= 1
