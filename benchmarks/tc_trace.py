@@ -9,9 +9,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
-CHAIN = [8, 9, 10, 1, 2, 3, 4, 11, 12, 7, 21, 22, 23, 13]
+CHAIN = [8, 9, 10, 1, 2, 3, 4, 11, 12, 7, 21, 27, 22]
 LABELS = {8: 'M wop', 9: 'M xfull', 10: 'M fwd', 1: 'E fwd done', 2: 'E part sent', 3: 'E p1 done', 4: 'E smax+bc',
-          11: 'M dl+p2', 12: 'M wgrad', 7: 'E wg done', 21: 'E db sync', 22: 'E optim', 23: 'E w out', 13: 'E publ'}
+          11: 'M dl+p2', 12: 'M wgrad', 7: 'E wg done', 21: 'E db sync', 27: 'E exch', 22: 'E optim'}
 
 
 def main():
@@ -32,13 +32,14 @@ def main():
     _lib.check(_lib.lib().pdm_net_tc_trace_read(buf.ctypes.data), 'pdm_net_tc_trace_read')
     print('batch {}: {:.2f} us/step by events (traced run)'.format(B, ms * 1e3 / 200))
     print('cycles since the CTA passed bar_wop (mean over steps 8..63)')
-    print('cta ' + ' '.join('{:>11s}'.format(LABELS[k]) for k in CHAIN) + '   period  P stored   P free')
+    print('cta ' + ' '.join('{:>11s}'.format(LABELS[k]) for k in CHAIN) + '   period  P stored   P free  publish')
     for c in range(13):
         steps = buf[c, 8:64]
         base = steps[:, 8]
         row = ' '.join('{:11.0f}'.format((steps[:, k] - base).mean()) for k in CHAIN)
         print('{:3d} {} {:8.0f} {:9.0f} {:8.0f}'.format(c, row, np.diff(steps[:, 13]).mean(), (steps[:, 18] - base).mean(),
-                                                     (steps[:, 17] - base).mean()))
+                                                     (steps[:, 17] - base).mean()) +
+              ' {:8.0f}'.format((steps[1:, 13] - steps[:-1, 22]).mean()))
     eng.close()
 
 
