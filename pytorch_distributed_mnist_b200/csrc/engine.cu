@@ -217,12 +217,14 @@ void worker_main(pdm_engine* e) {
 // The persistent tensor-core kernel (net_tc.cu) takes a whole pass in one launch: used for raw uint8
 // inputs whenever the device can launch it and the caller did not ask for a specific CTA count.
 // It runs on one 13-SM cluster, so beyond ~1024 rows per step the 148-SM per-step kernel is faster
-// (measured: 8.3 vs 9.6 us at batch 512, 57 vs 27 us at batch 4096; benchmarks/tc_sweep.py).  With peers its
-// in-kernel exchange wins up to PDM_NET_TC_MAX_WORLD GPUs (default 4; measured us/step: 2 GPUs 11.2 vs 12.7,
-// 4 GPUs 12.5 vs 14.0, 8 GPUs 17.9 vs 14.7) for resident inputs; passes that read pinned host memory always take it, for its feeder cluster
+// (measured: 7.7 vs 9.7 us at batch 512, 57 vs 27 us at batch 4096; benchmarks/tc_sweep.py).  With peers its
+// in-kernel exchange wins at every world size of one node (measured us/step at the 20-step pass of bench.py,
+// persistent vs per-step kernel: 2 GPUs 10.8 vs 13.8, 4 GPUs 12.5 vs 14.0, 8 GPUs 14.8 vs 15.4;
+// profiles/raw/r2/bench_*gpu_policy_k20.log).  PDM_NET_TC_MAX_WORLD (default 8) caps the world size that
+// takes it for resident inputs; passes that read pinned host memory always take it, for its feeder cluster
 // (8 GPUs: 21 vs 32 us/step).
 int tc_max_world() {
-  static const int v = [] { const char* e = getenv("PDM_NET_TC_MAX_WORLD"); return e && *e ? atoi(e) : 4; }();
+  static const int v = [] { const char* e = getenv("PDM_NET_TC_MAX_WORLD"); return e && *e ? atoi(e) : 8; }();
   return v;
 }
 bool use_tc(const pdm_engine* e, int x_dtype, int y_dtype, int ctas, int batch, bool from_host) {

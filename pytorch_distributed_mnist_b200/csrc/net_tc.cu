@@ -141,20 +141,8 @@ __device__ __forceinline__ long long clock_now() {
   return c;
 }
 // stamps go to shared memory (a global store per stamp perturbs what it measures) and are dumped at the end
-#ifndef PDM_TC_FORCE_STAMPS
-#define PDM_TC_FORCE_STAMPS 0      /* experiment knob: stamp in the production kernel too (1 epilogue, 2 MMA, 4 producer) */
-#endif
-#define TC_TRACE_IF(on, cond, step, slot) do { if ((on) && (cond) && (step) < kTraceSteps) \
+#define TC_TRACE(cond, step, slot) do { if (kTrace && (cond) && (step) < kTraceSteps) \
     reinterpret_cast<long long*>(smem + kOffTrace)[(step) * 32 + (slot)] = clock_now(); } while (0)
-#ifndef PDM_TC_MORE_SYNC
-#define PDM_TC_MORE_SYNC 0      /* experiment knob: extra reconvergence points (bit mask) */
-#endif
-#ifndef PDM_TC_FORCE_SLOTS
-#define PDM_TC_FORCE_SLOTS 0xffffffffu
-#endif
-#define TC_TRACE_E(cond, step, slot) TC_TRACE_IF(kTrace || ((PDM_TC_FORCE_STAMPS & 1) && ((PDM_TC_FORCE_SLOTS >> (slot)) & 1u)), cond, step, slot)
-#define TC_TRACE_M(cond, step, slot) TC_TRACE_IF(kTrace || (PDM_TC_FORCE_STAMPS & 2), cond, step, slot)
-#define TC_TRACE_P(cond, step, slot) TC_TRACE_IF(kTrace || (PDM_TC_FORCE_STAMPS & 4), cond, step, slot)
 
 // ---------------------------------------------------------------------------- PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -418,12 +406,12 @@ __device__ __forceinline__ void producer_loop(const TcArgs& a, uint8_t* smem, Mi
           }
         }
       }
-      TC_TRACE_P(pt == 32, step, 16);
+      TC_TRACE(pt == 32, step, 16);
       if (it > 0) {                                            // previous block's MMAs are done with the tile
         if (a.dbg & 1) mbar_wait(&ms->bar_wg, (it - 1) & 1u);
         else mbar_wait_relaxed(&ms->bar_wg, (it - 1) & 1u);
       }
-      TC_TRACE_P(pt == 32, step, 17);
+      TC_TRACE(pt == 32, step, 17);
 #pragma unroll
       for (int j = 0; j < kItems; ++j) {
         const int item = pt + kProdThreads * j;
@@ -449,7 +437,7 @@ __device__ __forceinline__ void producer_loop(const TcArgs& a, uint8_t* smem, Mi
         asm volatile("bar.sync 2, 224;" ::: "memory");
         if (pt == 0) flag_add_release(a.ring_flags + kRingSlots + (it % kRingSlots));
       }
-      TC_TRACE_P(pt == 32, step, 18);
+      TC_TRACE(pt == 32, step, 18);
     }
   }
 }
@@ -523,10 +511,10 @@ __device__ __forceinline__ void mma_loop(const TcArgs& a, uint8_t* smem, Misc* m
     mbar_wait(&ms->bar_wop, (uint32_t)step & 1u);              // this step's weights are in the B operand
     for (int blk = 0; blk < nblk; ++blk, ++it) {
       const Blk b = make_blk(n_step, blk);
-      TC_TRACE_M(true, step, 8);
+      TC_TRACE(true, step, 8);
       mbar_wait(&ms->bar_xfull, it & 1u);
       tc_fence_after();
-      TC_TRACE_M(true, step, 9);
+      TC_TRACE(true, step, 9);
       // ---- forward: [tile_rows x 48] = X[tile_rows x 64] . [W_hi; W_mid; W_lo]^T ----
       const int ntiles = b.tile_rows / 128;
       for (int mt = 0; mt < ntiles; ++mt) {
@@ -538,12 +526,12 @@ __device__ __forceinline__ void mma_loop(const TcArgs& a, uint8_t* smem, Misc* m
         }
       }
       umma_commit(&ms->bar_fwd);
-      TC_TRACE_M(true, step, 10);
+      TC_TRACE(true, step, 10);
       // ---- wgrad: G[(64 cols + ones + pad) x 48] (+)= X^T . [dl_hi | dl_mid | dl_lo] ----
       mbar_wait(&ms->bar_dl, it & 1u);                        // this CTA's own rows of the operand (and the forward accumulator is drained)
       mbar_wait(&ms->bar_p2, it & 1u);                        // the other CTAs' rows (bulk copies into the operand)
       tc_fence_after();
-      TC_TRACE_M(true, step, 11);
+      TC_TRACE(true, step, 11);
       const int ksteps = b.tile_rows / 16;
       for (int ks = 0; ks < ksteps; ++ks) {
         // MN-major, no swizzle: SBO = stride between 8-wide MN blocks, LBO = stride between 8-deep K groups
@@ -552,7 +540,7 @@ __device__ __forceinline__ void mma_loop(const TcArgs& a, uint8_t* smem, Misc* m
         umma_bf16(tmem_base + kTmemWg, da, db, kIdescWg, (!b.first || ks != 0) ? 1u : 0u);
       }
       umma_commit(&ms->bar_wg);
-      TC_TRACE_M(true, step, 12);
+      TC_TRACE(true, step, 12);
     }
   }
 }
@@ -589,7 +577,7 @@ __device__ __forceinline__ void ll_exchange(const TcArgs& a, uint8_t* smem, uint
     const float2 v = gbuf[u];
     ll_store2(a.peers.inbox[p] + ((par + me) * kCtas + cta) * kLLSlot + (size_t)u * 2, v.x, v.y, seq);
   }
-  TC_TRACE_E(t == 0, step, 24);
+  TC_TRACE(t == 0, step, 24);
   // poll: up to four units in flight per thread and round (eight spill registers into the hot loop) (one L2 round trip per round)
   constexpr int kInFlight = 4;
   for (int idx0 = t; idx0 < total; idx0 += kInFlight * kEpiThreads) {
@@ -629,9 +617,9 @@ __device__ __forceinline__ void ll_exchange(const TcArgs& a, uint8_t* smem, uint
       }
     }
   }
-  TC_TRACE_E(t == 0, step, 25);
+  TC_TRACE(t == 0, step, 25);
   epi_sync();
-  TC_TRACE_E(t == 0, step, 26);
+  TC_TRACE(t == 0, step, 26);
   {
     float sum[kHalf], sb = 0.f;
 #pragma unroll
@@ -741,7 +729,7 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
     tc_fence_before();
     mbar_arrive(&ms->bar_wop);
     epi_sync();
-    TC_TRACE_E(t == 0, step, 13);
+    TC_TRACE(t == 0, step, 13);
     const float2 adam_c = a.adam != nullptr ? __ldg(a.adam + step) : a.adam_inline[step];   // consumed at the end of the step
     float wsumn[kOut];
 #pragma unroll
@@ -759,10 +747,10 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
       }
 
       // ---- 1. partial logits of this CTA's 64 columns -> the rows' owners ----
-      TC_TRACE_E(t == 0, step, 0);
+      TC_TRACE(t == 0, step, 0);
       mbar_wait(&ms->bar_fwd, par);
       tc_fence_after();
-      TC_TRACE_E(t == 0, step, 1);
+      TC_TRACE(t == 0, step, 1);
       // staged in shared memory, then ONE bulk copy per owner: rows [40 o, 40 o + 40) are contiguous
       // and land in slot `cta` of owner o's exchange buffer
 #pragma unroll
@@ -789,16 +777,13 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
           bulk_s2s(mapa(xbuf_s + (uint32_t)(cta * kOwnRows * kOut) * 4u, (uint32_t)t), stage_s + (uint32_t)(t * kOwnRows * kOut) * 4u,
                    (uint32_t)(rows_o * kOut * 4), mapa(p1_s, (uint32_t)t));
       }
-#if PDM_TC_MORE_SYNC & 4
-      __syncwarp();
-#endif
       mbar_wait(&ms->bar_xfull, par);          // (long complete) acquire the producers' label stores
 
       // ---- 2. owner: two lanes per row (5 classes each): sum the 13 partials, soft-max, loss, top-1,
       //         dlogits as three bf16 terms straight into the wgrad operand ----
-      TC_TRACE_E(t == 0, step, 2);
+      TC_TRACE(t == 0, step, 2);
       mbar_wait(&ms->bar_p1, par);
-      TC_TRACE_E(t == 0, step, 3);
+      TC_TRACE(t == 0, step, 3);
       float my_loss = 0.f, my_hit = 0.f;
       {
         const int lr = t >> 1, half = t & 1;                 // lr < 64: rows beyond my_rows idle along (shuffles need every lane)
@@ -854,9 +839,6 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
           my_hit = beaten ? 0.f : 1.f;
         }
       }
-#if PDM_TC_MORE_SYNC & 2
-      __syncwarp();
-#endif
       if (warp < 3) {                                        // rows 0-15, 16-31, 32-39: fixed butterfly, deterministic
 #pragma unroll
         for (int o = 16; o >= 1; o >>= 1) {
@@ -878,12 +860,9 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
       if (t == 0)
         st_async2(mapa(smem_u32(&ms->lossbuf[cta][0]), 0u), (ms->lossw[0][0] + ms->lossw[1][0]) + ms->lossw[2][0],
                   (ms->lossw[0][1] + ms->lossw[1][1]) + ms->lossw[2][1], mapa(loss_s, 0u));
-#if PDM_TC_MORE_SYNC & 8
-      __syncwarp();
-#endif
       tc_fence_before();
       mbar_arrive(&ms->bar_dl);                              // own rows written, forward accumulator drained
-      TC_TRACE_E(t == 0, step, 4);
+      TC_TRACE(t == 0, step, 4);
 
       if (cta == 0 && t == 0) {                              // the step's metrics
         mbar_wait(&ms->bar_loss, par);
@@ -902,13 +881,10 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
         }
       }
 
-#if PDM_TC_MORE_SYNC & 1
-      __syncwarp();
-#endif
       // ---- 3. gradient of this CTA's columns, all-reduce, optimizer, next step's B operand ----
-      TC_TRACE_E(t == 0, step, 6);
+      TC_TRACE(t == 0, step, 6);
       mbar_wait(&ms->bar_wg, par);
-      TC_TRACE_E(t == 0, step, 7);
+      TC_TRACE(t == 0, step, 7);
       if (!b.last) continue;
       tc_fence_after();
       // accumulator row c holds column c's ten sums (row 64: the bias gradient): warps 0-1 keep classes 0-4 and
@@ -933,7 +909,7 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
         }
       }
       epi_sync();
-      TC_TRACE_E(t == 0, step, 21);
+      TC_TRACE(t == 0, step, 21);
       if (h == 1) {
 #pragma unroll
         for (int j = 0; j < kHalf; ++j) g[j] = xg[j * kCols + c];
@@ -942,7 +918,7 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
       for (int j = 0; j < kHalf; ++j) g[j] = owns_col ? fmaf(kScale, g[j], -kShift * ms->db[h * kHalf + j]) : 0.f;
       if (has_bias) gb = ms->db[t];
       if (a.peers.world > 1) ll_exchange<kTrace>(a, smem, a.peers.seq + (uint32_t)step, step, cta, t, g, gb);
-      TC_TRACE_E(t == 0, step, 27);
+      TC_TRACE(t == 0, step, 27);
       {
         const float step_size = adam_c.x, inv_bc2 = adam_c.y;
         const bool first = a.step0 + step <= 1;
@@ -974,7 +950,7 @@ __device__ __forceinline__ void epilogue_loop(const TcArgs& a, uint8_t* smem, Mi
           }
         }
       }
-      TC_TRACE_E(t == 0, step, 22);
+      TC_TRACE(t == 0, step, 22);
       // Reconverge here: the guarded stores above leave the warp split, and without this the next step's
       // publish code runs once per fragment (measured on the same box: 7.76 -> 7.30 us/step at batch 512).
       __syncwarp();

@@ -162,6 +162,7 @@ def _tc_worker(rank, world, port):
     from pytorch_distributed_mnist_b200 import Net, FusedAdam, DistributedDataParallel
     from pytorch_distributed_mnist_b200.ops import net_tc
     from pytorch_distributed_mnist_b200.ops.engine import NetEngine
+    os.environ['PDM_NET_TC_MAX_WORLD'] = '8'          # whatever the policy default: this test is about the kernel
     _init(rank, world, port)
     try:
         dev = torch.device('cuda', rank)
