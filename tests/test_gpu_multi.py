@@ -147,8 +147,9 @@ def _assert_close_after_adam(a, b, lr, steps):
     visible fraction of lr for a handful of elements.  Compare the bulk tightly and bound the outliers:
     measured on B200, 4 steps: mean drift ~1e-7, 4 of 1.18 M elements above 2e-4 (max 3.8e-4) at 8 GPUs."""
     d = (a.detach() - b.detach()).abs()
-    # bounds a few times what was measured (passes at 2 and 8 GPUs: profiles/raw/r2/): a reducer or slicing
-    # bug that touches even a hundred elements fails here
+    # bounds a few times what was measured at 8 GPUs (the worst case); run with these bounds at 2 GPUs
+    # (profiles/raw/r2/pytest_gpu_2gpus_native_reducer.log): a reducer or slicing bug that touches even a
+    # hundred elements fails here
     assert d.max().item() <= 1e-3, 'max drift {:.3e}'.format(d.max().item())
     assert d.mean().item() < 2e-6, 'mean drift {:.3e}'.format(d.mean().item())
     outliers = int((d > 2e-4 + 2e-3 * b.detach().abs()).sum().item())
