@@ -419,6 +419,11 @@ int pdm_reducer_create(pdm_reducer** out, const pdm_reducer_config* cfg);
 int pdm_reducer_arm(pdm_reducer* r);   /* start of a training forward; PDM_ERR_STATE if the last pass is unfinished */
 int pdm_reducer_mark_ready(pdm_reducer* r, int32_t param, const pdm_hyper* hyper, pdm_stream_t compute,
                            pdm_stream_t comm_stream, int32_t* first, int32_t* count);
+/* find_unused_parameters: list the parameters without a gradient in this pass (zero their slices), then
+ * finalize marks them ready and launches the remaining buckets. */
+int pdm_reducer_unmarked(pdm_reducer* r, int32_t* out, int32_t* count);
+int pdm_reducer_finalize(pdm_reducer* r, const pdm_hyper* hyper, pdm_stream_t compute, pdm_stream_t comm_stream,
+                         int32_t* first, int32_t* count);
 int pdm_reducer_state(pdm_reducer* r, int32_t* next, int64_t* launches, int32_t* pending, int32_t* order,
                       int32_t* n_order);
 int pdm_reducer_destroy(pdm_reducer* r);

@@ -155,6 +155,45 @@ extern "C" int pdm_reducer_mark_ready(pdm_reducer* r, int32_t param, const pdm_h
   return PDM_OK;
 }
 
+// Parameters that have not been marked in this pass (find_unused_parameters: the caller zeroes their
+// gradient slices, then calls pdm_reducer_finalize).  out may be NULL to get the count only.
+extern "C" int pdm_reducer_unmarked(pdm_reducer* r, int32_t* out, int32_t* count) {
+  PDM_REQUIRE(r && count, PDM_ERR_ARG, "pdm_reducer_unmarked: bad arguments");
+  int32_t n = 0;
+  for (int i = 0; i < r->n_params; ++i) {
+    if (r->marked[i]) continue;
+    if (out) out[n] = i;
+    n += 1;
+  }
+  *count = n;
+  return PDM_OK;
+}
+
+// End of a backward pass in find_unused_parameters mode: every parameter that received no gradient counts
+// as ready (its slice holds zeros), so the remaining buckets go out -- in index order, on every rank, whatever
+// subset of the model each rank used.  A pass that marked nothing launches nothing.
+extern "C" int pdm_reducer_finalize(pdm_reducer* r, const pdm_hyper* hyper, pdm_stream_t compute,
+                                    pdm_stream_t comm_stream, int32_t* first, int32_t* count) {
+  PDM_REQUIRE(r, PDM_ERR_ARG, "pdm_reducer_finalize: null reducer");
+  int f = r->next, c = 0;
+  if (r->started) {
+    for (int i = 0; i < r->n_params; ++i) {
+      if (r->marked[i]) continue;
+      r->marked[i] = 1;
+      r->pending[r->bucket_of[i]] -= 1;
+    }
+    while (r->next < r->n_buckets && r->pending[r->next] == 0) {
+      int rc = launch_bucket(r, r->next, hyper, compute, comm_stream);
+      if (rc != PDM_OK) return rc;
+      r->next += 1;
+      c += 1;
+    }
+  }
+  if (first) *first = f;
+  if (count) *count = c;
+  return PDM_OK;
+}
+
 // next bucket to launch, total launches so far; pending[n_buckets] and order[<= n_buckets] are optional.
 extern "C" int pdm_reducer_state(pdm_reducer* r, int32_t* next, int64_t* launches, int32_t* pending, int32_t* order,
                                  int32_t* n_order) {

@@ -120,9 +120,13 @@ class DistributedDataParallel(nn.Module):
                  gradient_as_bucket_view=True, static_graph=False):
         super().__init__()
         # accepted for drop-in compatibility with torch's constructor (ref:188-189 passes only device_ids)
-        if find_unused_parameters:
-            raise NotImplementedError('find_unused_parameters=True is not supported: gradients are produced straight '
-                                      'into bucket memory and every parameter must receive one (see _arm)')
+        # find_unused_parameters=True: at the end of every backward pass the parameters that received no
+        # gradient are given a zero gradient and counted as ready, so every bucket is still reduced, in
+        # order, on every rank (the ranks may have used different parts of the model).  Difference to the
+        # stock wrapper: a parameter NO rank used gets a zero gradient rather than none, so a fused Adam
+        # still decays its moments; with plain SGD the two are identical.  Every rank's loss must depend on
+        # at least one parameter.
+        self.find_unused_parameters = bool(find_unused_parameters)
         if not gradient_as_bucket_view:
             raise NotImplementedError('gradients are always views of the flat bucket memory here '
                                       '(gradient_as_bucket_view=False would add the copies this design removes)')
@@ -228,6 +232,7 @@ class DistributedDataParallel(nn.Module):
             if region is not None else None,
             device=(self.device.index or 0) if region is not None else -1)
         self._hyper = None
+        self._finalize_queued = False
         self.require_backward_grad_sync = True
         self._hooks = []
         for i, p in enumerate(params):
@@ -294,10 +299,11 @@ class DistributedDataParallel(nn.Module):
             raise RuntimeError(
                 'DistributedDataParallel: the previous backward pass did not produce gradients for every parameter '
                 '(buckets {}..{} were never reduced; parameters without a gradient are among indices {}). Every '
-                'parameter must take part in the loss (there is no find_unused_parameters mode), or wrap the '
-                'extra forward passes in no_sync() / torch.no_grad().'.format(
+                'parameter must take part in the loss (or construct the wrapper with find_unused_parameters=True), '
+                'or wrap the extra forward passes in no_sync() / torch.no_grad().'.format(
                     st['next'], len(self.buckets) - 1, missing[:8]))
         self._hyper = None
+        self._finalize_queued = False
         self.flat.attach_grads()
 
     class _NoSync(object):
@@ -325,6 +331,10 @@ class DistributedDataParallel(nn.Module):
                 # autograd installed its own tensor (grad was None): move it into the bucket
                 flat.view_of('grads', index).copy_(param.grad)
                 param.grad = flat.view_of('grads', index)
+            if self.find_unused_parameters and not self._finalize_queued:
+                # runs once autograd has finished this backward pass
+                self._finalize_queued = True
+                torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
             if self.uses_peer:
                 if self._hyper is None and self.fuse_optimizer and flat.optimizer is not None:
                     self._hyper = flat.optimizer.hyper(flat.optimizer.step_count + 1)
@@ -335,6 +345,31 @@ class DistributedDataParallel(nn.Module):
             for b in range(first, first + count):
                 self._after_launch(b) if self.uses_peer else self._reduce_with_group(b)
         return hook
+
+    def _finalize_backward(self):
+        """``find_unused_parameters``: zero the gradient of every parameter autograd did not reach, then let
+        the native reducer count them as ready and launch the remaining buckets."""
+        self._finalize_queued = False
+        if not self.require_backward_grad_sync:
+            return
+        flat = self.flat
+        unused = self._reducer.unmarked()
+        if not unused:
+            return
+        self.stats['unused_parameters'] = len(unused)
+        with torch.no_grad():
+            for i in unused:
+                flat.view_of('grads', i).zero_()
+                p = flat.param_list[i]
+                if p.grad is None or p.grad.data_ptr() != flat.view_of('grads', i).data_ptr():
+                    p.grad = flat.view_of('grads', i)
+        if self.uses_peer:
+            first, count = self._reducer.finalize(self._hyper, torch.cuda.current_stream(self.device).cuda_stream,
+                                                  self.comm_stream.cuda_stream)
+        else:
+            first, count = self._reducer.finalize()
+        for b in range(first, first + count):
+            self._after_launch(b) if self.uses_peer else self._reduce_with_group(b)
 
     def _after_launch(self, b):
         """Bookkeeping for a bucket the native reducer launched on the communication stream."""

@@ -48,6 +48,16 @@ def _d4(fn):
                    ctypes.POINTER(ctypes.c_int32)]
 
 
+@_lib.optional_decl('pdm_reducer_unmarked')
+def _d6(fn):
+    fn.argtypes = [c_void_p, c_void_p, ctypes.POINTER(ctypes.c_int32)]
+
+
+@_lib.optional_decl('pdm_reducer_finalize')
+def _d7(fn):
+    fn.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
+
+
 @_lib.optional_decl('pdm_reducer_destroy')
 def _d5(fn):
     fn.argtypes = [c_void_p]
@@ -86,6 +96,21 @@ class NativeReducer(object):
         _lib.check(self._lib.pdm_reducer_mark_ready(self._h, int(index), ctypes.byref(hyper) if hyper is not None else None,
                                                     compute_stream, comm_stream, ctypes.byref(self._first),
                                                     ctypes.byref(self._count)), 'pdm_reducer_mark_ready')
+        return self._first.value, self._count.value
+
+    def unmarked(self):
+        """Indices of the parameters that received no gradient in this pass so far."""
+        out = (ctypes.c_int32 * self.n_params)()
+        n = ctypes.c_int32(0)
+        _lib.check(self._lib.pdm_reducer_unmarked(self._h, out, ctypes.byref(n)), 'pdm_reducer_unmarked')
+        return list(out)[:n.value]
+
+    def finalize(self, hyper=None, compute_stream=0, comm_stream=0):
+        """End of a backward pass (``find_unused_parameters``): count the unmarked parameters as ready and
+        launch the remaining buckets.  Returns ``(first, count)`` like ``mark_ready``."""
+        _lib.check(self._lib.pdm_reducer_finalize(self._h, ctypes.byref(hyper) if hyper is not None else None,
+                                                  compute_stream, comm_stream, ctypes.byref(self._first),
+                                                  ctypes.byref(self._count)), 'pdm_reducer_finalize')
         return self._first.value, self._count.value
 
     def state(self):

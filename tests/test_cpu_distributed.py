@@ -268,3 +268,59 @@ def test_buffers_are_rebroadcast_each_training_forward(tmp_path, free_port):
     ddp = pdm.DistributedDataParallel(net)
     ddp(torch.randn(4, 3)).sum().backward()                 # world == 1: no-op path must not touch anything
     assert int(net[1].num_batches_tracked) == 1
+
+
+class _TwoBranch(torch.nn.Module):
+    """Each forward uses branch ``a`` or branch ``b``; ``never`` is not used at all."""
+
+    def __init__(self):
+        super().__init__()
+        self.a = torch.nn.Linear(600, 500)        # 1.2 MB each: two buckets
+        self.b = torch.nn.Linear(600, 500)
+        self.c = torch.nn.Linear(500, 4)
+        self.never = torch.nn.Linear(3, 3)
+
+    def forward(self, x, use_b):
+        return self.c(torch.relu(self.b(x) if use_b else self.a(x)))
+
+
+def _unused_worker(rank, world, port, out_dir):
+    import pytorch_distributed_mnist_b200 as pdm
+    dist.init_process_group('gloo', init_method='tcp://127.0.0.1:{}'.format(port), world_size=world, rank=rank)
+    try:
+        torch.manual_seed(5)
+        ours = pdm.DistributedDataParallel(_TwoBranch(), find_unused_parameters=True, bucket_cap_mb=1)
+        torch.manual_seed(5)
+        stock_mod = _TwoBranch()
+        stock = torch.nn.parallel.DistributedDataParallel(stock_mod, find_unused_parameters=True)
+        assert len(ours.buckets) >= 2
+        o_opt = pdm.FusedSGD(ours.parameters(), lr=0.05)
+        s_opt = torch.optim.SGD(stock.parameters(), lr=0.05)
+        g = torch.Generator().manual_seed(11 + rank)
+        for i in range(4):
+            x = torch.randn(16, 600, generator=g)
+            y = torch.randint(0, 4, (16,), generator=g)
+            use_b = (i + rank) % 2 == 1                    # the ranks use different branches in the same step
+            for m, o in ((ours, o_opt), (stock, s_opt)):
+                o.zero_grad()
+                torch.nn.functional.cross_entropy(m(x, use_b), y).backward()
+                o.step()
+        for (n, a), b in zip(ours.module.named_parameters(), stock_mod.parameters()):
+            torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-6, msg=lambda m, n=n: n + ': ' + m)
+        st = ours._reducer.state()
+        assert st['launches'] == 4 * len(ours.buckets) and st['next'] == len(ours.buckets)
+        assert ours.stats['unused_parameters'] == 4        # one branch (weight + bias) and `never`
+        torch.save({k: v for k, v in ours.state_dict().items()}, os.path.join(out_dir, 'rank{}.pt'.format(rank)))
+        ours.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_find_unused_parameters_matches_stock_ddp(tmp_path, free_port):
+    """parameters without a gradient are counted as ready at the end of the backward pass by the
+    native reducer; every bucket is still reduced on every rank although the ranks used different branches."""
+    mp.spawn(_unused_worker, args=(2, free_port, str(tmp_path)), nprocs=2)
+    a = torch.load(str(tmp_path / 'rank0.pt'))
+    b = torch.load(str(tmp_path / 'rank1.pt'))
+    for k in a:
+        assert torch.equal(a[k], b[k]), 'replicas diverged: ' + k
