@@ -88,3 +88,43 @@ def test_net_forward_module_uses_native_kernel():
     torch.testing.assert_close(out, ref, rtol=1e-4, atol=1e-4)
     out.sum().backward()
     assert net.fc.weight.grad is not None and net.fc.bias.grad is not None
+
+
+def test_find_unused_parameters_on_the_peer_path():
+    """The native reducer's end-of-backward pass on a GPU: the branch that received no gradient is counted
+    as ready, every bucket kernel still runs (fused SGD inside), parameters follow torch.optim.SGD."""
+    import pytorch_distributed_mnist_b200 as pdm
+
+    class TwoBranch(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.a = torch.nn.Linear(600, 500)
+            self.b = torch.nn.Linear(600, 500)
+            self.c = torch.nn.Linear(500, 4)
+            self.never = torch.nn.Linear(3, 3)
+
+        def forward(self, x, use_b):
+            return self.c(torch.relu(self.b(x) if use_b else self.a(x)))
+
+    torch.manual_seed(5)
+    ours = pdm.DistributedDataParallel(TwoBranch().cuda(), device_ids=[0], find_unused_parameters=True, bucket_cap_mb=1)
+    torch.manual_seed(5)
+    ref = TwoBranch().cuda()
+    assert ours.uses_peer and len(ours.buckets) >= 2
+    o_opt = pdm.FusedSGD(ours.parameters(), lr=0.05)
+    r_opt = torch.optim.SGD(ref.parameters(), lr=0.05)
+    g = torch.Generator().manual_seed(11)
+    for i in range(4):
+        x = torch.randn(16, 600, generator=g).cuda()
+        y = torch.randint(0, 4, (16,), generator=g).cuda()
+        for m, o in ((ours, o_opt), (ref, r_opt)):
+            o.zero_grad()
+            F.cross_entropy(m(x, i % 2 == 1), y).backward()
+            o.step()
+    torch.cuda.synchronize()
+    for (n, a), b in zip(ours.module.named_parameters(), ref.parameters()):
+        torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5, msg=lambda m, n=n: n + ': ' + m)
+    st = ours._reducer.state()
+    assert ours._reducer.native_comm and st['launches'] == 4 * len(ours.buckets)
+    assert ours.stats['unused_parameters'] == 4
+    ours.close()
