@@ -192,7 +192,7 @@ def run_ours(opts):
     pool_y = torch.randint(0, 10, (POOL_BATCHES * B,), dtype=torch.uint8, device=device, generator=g)
 
     with ClockSampler(local) as clocks:
-        # ---- value: K steps, inputs resident, one launch per step ----
+        # ---- value: K steps, inputs resident (one launch for the whole pass when the persistent kernel takes it) ----
         sync_all(dist, device)
         engine.train_device(pool_x, pool_y, B, max(W, 3), ctas=opts.ctas)
         sync_all(dist, device)
@@ -246,10 +246,13 @@ def run_ours(opts):
                            else ('single GPU' if world == 1 else 'torch.distributed fallback'),
                    'l2_policy': 'inputs larger than L2: {} distinct batches = {:.0f} MB cycled'.format(
                        POOL_BATCHES, POOL_BATCHES * B * 785 / 1e6),
-                   'inputs': 'raw uint8 pixels, normalised in-kernel (bit-exact ToTensor+Normalize); fp32 math'},
+                   'inputs': 'raw uint8 pixels, normalised in-kernel (bit-exact ToTensor+Normalize); fp32 math',
+                   'kernel': ('persistent tcgen05 cluster kernel, one launch for the K steps (csrc/net_tc.cu; bf16 operand '
+                              'terms with exact products, fp32 accumulation in TMEM)' if launches == 1 and K > 1
+                              else 'per-step fused FMA kernel, one launch per step (csrc/net_step.cu)')},
         'wall_ms_per_step': wall_ms / K,
         'fp32_inputs': {'value': images / (ms_f32 / 1e3), 'ms_per_step': ms_f32 / K,
-                        'note': 'same kernel instantiated for already-normalised fp32 pixels + int64 labels, the bytes '
+                        'note': 'the per-step FMA kernel (csrc/net_step.cu) on already-normalised fp32 pixels + int64 labels, the bytes '
                                 'the reference arm reads (3,144 B/sample); {} distinct batches = {:.0f} MB cycled'.format(
                                     nb32, nb32 * B * 3144 / 1e6)},
         'clocks': clk,
