@@ -424,6 +424,9 @@ int pdm_reducer_mark_ready(pdm_reducer* r, int32_t param, const pdm_hyper* hyper
 int pdm_reducer_unmarked(pdm_reducer* r, int32_t* out, int32_t* count);
 int pdm_reducer_finalize(pdm_reducer* r, const pdm_hyper* hyper, pdm_stream_t compute, pdm_stream_t comm_stream,
                          int32_t* first, int32_t* count);
+/* Order in which the parameters became ready in this pass, and whether a completed bucket had to wait for
+ * an earlier one (input of the bucket rebuild after the first iteration). */
+int pdm_reducer_ready_order(pdm_reducer* r, int32_t* out, int32_t* n, int32_t* held_back);
 int pdm_reducer_state(pdm_reducer* r, int32_t* next, int64_t* launches, int32_t* pending, int32_t* order,
                       int32_t* n_order);
 int pdm_reducer_destroy(pdm_reducer* r);

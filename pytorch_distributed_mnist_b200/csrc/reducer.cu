@@ -23,6 +23,8 @@ struct pdm_reducer {
   std::vector<int32_t> pending;         // parameters still missing in this pass
   std::vector<uint8_t> marked;          // parameter already seen in this pass
   std::vector<int32_t> order;           // launch log of this pass
+  std::vector<int32_t> ready;           // parameters in the order they became ready in this pass
+  bool held_back = false;               // a bucket completed while an earlier one was still open
   int next = 0;                         // next bucket to launch
   bool started = false;                 // a parameter was marked since the last arm
   size_t grads_off = 0, params_off = 0, m_off = 0, v_off = 0;
@@ -92,6 +94,8 @@ extern "C" int pdm_reducer_arm(pdm_reducer* r) {
   r->pending = r->size;
   std::fill(r->marked.begin(), r->marked.end(), 0);
   r->order.clear();
+  r->ready.clear();
+  r->held_back = false;
   r->next = 0;
   r->started = false;
   return PDM_OK;
@@ -141,8 +145,10 @@ extern "C" int pdm_reducer_mark_ready(pdm_reducer* r, int32_t param, const pdm_h
               "(two backward passes after one forward? wrap the extra ones in no_sync())", (int)param);
   r->marked[param] = 1;
   r->started = true;
+  r->ready.push_back(param);
   const int b = r->bucket_of[param];
   r->pending[b] -= 1;
+  if (r->pending[b] == 0 && b > r->next) r->held_back = true;
   int f = r->next, c = 0;
   while (r->next < r->n_buckets && r->pending[r->next] == 0) {
     int rc = launch_bucket(r, r->next, hyper, compute, comm_stream);
@@ -180,6 +186,7 @@ extern "C" int pdm_reducer_finalize(pdm_reducer* r, const pdm_hyper* hyper, pdm_
     for (int i = 0; i < r->n_params; ++i) {
       if (r->marked[i]) continue;
       r->marked[i] = 1;
+      r->ready.push_back(i);
       r->pending[r->bucket_of[i]] -= 1;
     }
     while (r->next < r->n_buckets && r->pending[r->next] == 0) {
@@ -191,6 +198,17 @@ extern "C" int pdm_reducer_finalize(pdm_reducer* r, const pdm_hyper* hyper, pdm_
   }
   if (first) *first = f;
   if (count) *count = c;
+  return PDM_OK;
+}
+
+// The order in which the parameters became ready in this pass (out: n_params entries, *n = how many so
+// far) and whether a bucket had to wait for an earlier one: the input of the bucket rebuild after the
+// first iteration (c10d Reducer::rebuild_buckets).
+extern "C" int pdm_reducer_ready_order(pdm_reducer* r, int32_t* out, int32_t* n, int32_t* held_back) {
+  PDM_REQUIRE(r && n, PDM_ERR_ARG, "pdm_reducer_ready_order: bad arguments");
+  if (out) std::copy(r->ready.begin(), r->ready.end(), out);
+  *n = (int32_t)r->ready.size();
+  if (held_back) *held_back = r->held_back ? 1 : 0;
   return PDM_OK;
 }
 

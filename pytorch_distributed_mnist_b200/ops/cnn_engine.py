@@ -81,6 +81,7 @@ class CnnEngine(object):
         _lib.check(self._lib.pdm_cnn_create(ctypes.byref(self._h), self.device.index or 0, cnn.width, int(max_batch)),
                    'pdm_cnn_create')
         self.max_batch = int(max_batch)
+        flat.layout_frozen = True      # raw pointers into the layout are captured below
         self.params = CnnParams(*[flat.view_of('params', i).data_ptr() for i in range(8)])
         self.grads = CnnParams(*[flat.view_of('grads', i).data_ptr() for i in range(8)])
         self.metrics = torch.zeros(4, dtype=torch.float64, device=self.device)

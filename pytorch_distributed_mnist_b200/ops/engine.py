@@ -23,6 +23,7 @@ class NetEngine(object):
             raise ValueError('NetEngine drives the reference Net only (flat size {}, expected {})'
                              .format(flat.numel, _lib.NET_FLAT))
         self.flat = flat
+        flat.layout_frozen = True      # the native engine works on raw pointers into this layout
         self.optimizer = optimizer
         self.comm = comm
         self.device = torch.device(device if device is not None else flat.params.device)

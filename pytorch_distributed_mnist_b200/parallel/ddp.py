@@ -25,7 +25,13 @@ launches (K11)                         comm stream does all-reduce + 1/W +
 =====================================  =======================================
 
 Buckets are launched strictly in index order on every rank (same rule as the
-Reducer), so all ranks issue the same collective sequence.
+Reducer), so all ranks issue the same collective sequence.  The bookkeeping, the
+stream ordering and the kernel launches are native (``csrc/reducer.cu``); this
+module forwards autograd's post-accumulate hook.  After the first complete
+backward pass the buckets are regrouped once in the observed gradient-ready
+order when that changes the schedule (``_maybe_rebuild_buckets``, the role of
+``Reducer::rebuild_buckets``); ``find_unused_parameters=True`` counts parameters
+without a gradient as ready at the end of backward (``_finalize_backward``).
 
 Fallback: without the peer communicator (CPU/gloo, or GPUs without P2P) buckets
 are all-reduced with ``torch.distributed`` and ``optimizer.step()`` applies the
@@ -117,7 +123,7 @@ class DistributedDataParallel(nn.Module):
     def __init__(self, module, device_ids=None, output_device=None, broadcast_buffers=True,
                  bucket_cap_mb=DEFAULT_BUCKET_CAP_MB, comm='auto', fuse_optimizer=True,
                  comm_timeout_s=30.0, process_group=None, store=None, find_unused_parameters=False,
-                 gradient_as_bucket_view=True, static_graph=False):
+                 gradient_as_bucket_view=True, static_graph=False, rebuild_buckets=True):
         super().__init__()
         # accepted for drop-in compatibility with torch's constructor (ref:188-189 passes only device_ids)
         # find_unused_parameters=True: at the end of every backward pass the parameters that received no
@@ -130,7 +136,7 @@ class DistributedDataParallel(nn.Module):
         if not gradient_as_bucket_view:
             raise NotImplementedError('gradients are always views of the flat bucket memory here '
                                       '(gradient_as_bucket_view=False would add the copies this design removes)')
-        del static_graph        # the bucket schedule is static by construction
+        del static_graph        # nothing to specialise: the schedule is fixed after the one bucket rebuild
         self.module = module
         params = [p for p in module.parameters() if p.requires_grad]
         if not params:
@@ -209,35 +215,90 @@ class DistributedDataParallel(nn.Module):
                 dist.broadcast(b, 0, group=process_group)
 
         # -- buckets + hooks -------------------------------------------------
+        self._bucket_cap_bytes = int(bucket_cap_mb * 1024 * 1024)
+        self._works = []
+        self.comm_stream = torch.cuda.Stream(device=self.device) if self.device.type == 'cuda' else None
+        self._reducer = None
+        self._rebuilt = not rebuild_buckets  # the bucket rebuild runs at most once, after the first complete pass
+        self._build_buckets()
+        self.require_backward_grad_sync = True
+        self._hooks = []
+        for i, p in enumerate(params):
+            self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(i)))
+        self.stats = {'bucket_launches': 0, 'bucket_bytes': [4 * (bk['hi'] - bk['lo']) for bk in self.buckets]}
+
+    # -- buckets ----------------------------------------------------------------
+    def _build_buckets(self):
+        """Bucket assignment over the flat buffer's CURRENT memory order (N5) and a native reducer for it:
+        the reducer (csrc/reducer.cu) counts readiness, orders the streams and launches the fused bucket
+        kernels; without a native communicator it reports the buckets to reduce here."""
+        from .reducer import NativeReducer
+        flat = self.flat
+        params = flat.param_list
         self.buckets = []
-        for idxs in assign_buckets([p.numel() for p in params], cap_bytes=int(bucket_cap_mb * 1024 * 1024)):
-            lo, hi = self.flat.range_of(min(idxs), max(idxs))
-            self.buckets.append({'params': idxs, 'lo': lo, 'hi': hi})
+        for pos in assign_buckets([params[i].numel() for i in flat.layout], cap_bytes=self._bucket_cap_bytes):
+            lo, hi = flat.range_of(min(pos), max(pos))
+            self.buckets.append({'params': [flat.layout[j] for j in pos], 'lo': lo, 'hi': hi})
         self._bucket_of = {}
         for b, bk in enumerate(self.buckets):
             for i in bk['params']:
                 self._bucket_of[i] = b
-        self._works = []
-        self.comm_stream = torch.cuda.Stream(device=self.device) if self.device.type == 'cuda' else None
-        # the native reducer (csrc/reducer.cu) counts readiness, orders the streams and launches the
-        # fused bucket kernels; without a native communicator it reports the buckets to reduce here
-        from .reducer import NativeReducer
+        if self._reducer is not None:
+            self._reducer.close()
         region = self.nvls if self.nvls is not None else (self.comm if self.uses_peer else None)
         self._reducer = NativeReducer(
             [self._bucket_of[i] for i in range(len(params))], [(bk['lo'], bk['hi']) for bk in self.buckets],
             world=self.world,
             comm_handle=self.comm.handle if (self.uses_peer and self.nvls is None) else None,
             nvls_handle=self.nvls.handle if self.nvls is not None else None,
-            offsets=[region.offset_of(getattr(self.flat, n)) for n in ('grads', 'params', 'exp_avg', 'exp_avg_sq')]
+            offsets=[region.offset_of(getattr(flat, n)) for n in ('grads', 'params', 'exp_avg', 'exp_avg_sq')]
             if region is not None else None,
             device=(self.device.index or 0) if region is not None else -1)
         self._hyper = None
         self._finalize_queued = False
-        self.require_backward_grad_sync = True
-        self._hooks = []
-        for i, p in enumerate(params):
-            self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(i)))
-        self.stats = {'bucket_launches': 0, 'bucket_bytes': [4 * (bk['hi'] - bk['lo']) for bk in self.buckets]}
+        if hasattr(self, 'stats'):
+            self.stats['bucket_bytes'] = [4 * (bk['hi'] - bk['lo']) for bk in self.buckets]
+
+    def _maybe_rebuild_buckets(self):
+        """The role of ``Reducer::rebuild_buckets``: after the first complete backward pass, regroup the
+        parameters in the order their gradients actually became ready (rank 0's order, like the stock
+        wrapper) -- but only when that changes the schedule, i.e. when a finished bucket had to wait for an
+        earlier one.  A bucket is a contiguous range of the flat buffer, so regrouping MOVES the parameters
+        (``FlatState.relayout``); feed-forward models registered in call order never need it."""
+        if self._rebuilt:
+            return
+        order, held_back = self._reducer.ready_order()
+        if len(order) != len(self.flat.param_list):
+            return                                   # no complete pass yet
+        self._rebuilt = True
+        decision = (order if held_back and not self.flat.layout_frozen else [])
+        if self.world > 1:
+            # rank 0 decides for everybody (the ranks may have seen different orders)
+            if self._meta_store is not None:
+                if self.rank == 0:
+                    self._meta_store.set(self._tag + '/rebuild', ','.join(str(i) for i in decision).encode())
+                raw = bytes(self._meta_store.get(self._tag + '/rebuild')).decode()
+                decision = [int(v) for v in raw.split(',')] if raw else []
+            else:
+                box = [decision]
+                dist.broadcast_object_list(box, src=0, group=self._process_group)
+                decision = box[0]
+        if not decision:
+            return
+        if self.flat.layout_frozen:
+            raise RuntimeError('rank 0 asked for a bucket rebuild but a native engine on this rank holds the layout')
+        self.flat.consolidate(self._process_group)   # collective; no-op unless the optimizer state is sharded
+        if self.device.type == 'cuda':
+            torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            dist.barrier(group=self._process_group)  # no peer may still be reading the old layout
+        # memory order = reverse ready order: the bucket walk goes back to front, so bucket 0 holds the
+        # gradients that arrive first
+        self.flat.relayout(list(reversed(decision)))
+        self._build_buckets()
+        self.stats['rebuilt'] = 1
+        if self.world > 1:
+            dist.barrier(group=self._process_group)
 
     # -- K14 -------------------------------------------------------------------
     def _verify_params(self, params, group):
@@ -292,6 +353,7 @@ class DistributedDataParallel(nn.Module):
         # Stock DDP refuses to start an iteration when the previous one did not finish its reduction
         # ("Expected to have finished reduction in the prior iteration"): a parameter that received no
         # gradient leaves its bucket -- and every later one -- unreduced, and the ranks drift apart.
+        self._maybe_rebuild_buckets()
         if not self._reducer.arm():
             st = self._reducer.state()
             missing = [i for b in range(st['next'], len(self.buckets)) for i in self.buckets[b]['params']

@@ -14,6 +14,8 @@ its ``.grad`` and its optimizer state are views into it.  Consequences:
 Layout rule: parameters in ``module.parameters()`` order, each starting on a
 4-float (16-byte) boundary; for ``Net`` this gives exactly the
 ``PDM_NET_FLAT`` layout of ``include/pdmnist.h`` (weight at 0, bias at 7840).
+``relayout`` moves them into another order (the reducer's bucket rebuild); the
+native engines freeze the layout they were built on.
 
 Sharded optimizer state.  The two-shot form of the fused all-reduce + optimizer
 (``csrc/comm.cu``, buckets >= 256 KB) lets rank r update only slice r of a
@@ -53,6 +55,8 @@ class FlatState(object):
         for p in params:
             self.offsets.append(off)
             off = _round_up(off + p.numel(), 4)
+        self.layout = list(range(len(params)))        # parameter indices in memory order (see relayout)
+        self.layout_frozen = False                    # set by the native engines, which hold raw pointers into the layout
         self.numel = off                              # floats, multiple of 4
         self.section = _round_up(self.numel, 64)      # section stride (256-byte aligned)
         self.comm = comm
@@ -93,10 +97,48 @@ class FlatState(object):
         self.grads.zero_()
 
     def range_of(self, first, last):
-        """Float range [lo, hi) covering parameters first..last (inclusive), 4-aligned."""
-        lo = self.offsets[first]
-        hi = _round_up(self.offsets[last] + self.param_list[last].numel(), 4)
+        """Float range [lo, hi) covering the parameters at memory positions first..last (inclusive),
+        4-aligned.  Positions index ``self.layout``; without a relayout they are the parameter indices."""
+        a, b = self.layout[first], self.layout[last]
+        lo = self.offsets[a]
+        hi = _round_up(self.offsets[b] + self.param_list[b].numel(), 4)
         return lo, hi
+
+    def relayout(self, layout):
+        """Move the parameters (with gradients and optimizer state) into a new memory order: ``layout``
+        lists the parameter indices front to back.  Used by the reducer's bucket rebuild: a
+        bucket is a contiguous range, so regrouping parameters means moving them.  Every view handed out
+        before (``p.data``, ``p.grad``, optimizer state) is re-created; call ``consolidate`` first when
+        the optimizer state is sharded."""
+        layout = [int(i) for i in layout]
+        n = len(self.param_list)
+        if sorted(layout) != list(range(n)):
+            raise ValueError('relayout needs a permutation of 0..{}'.format(n - 1))
+        if self.layout_frozen:
+            raise RuntimeError('a native engine holds pointers into this layout; it cannot be changed')
+        if self.state_stale:
+            raise RuntimeError('consolidate() the sharded optimizer state before a relayout')
+        new_off, off = [0] * n, 0
+        for i in layout:
+            new_off[i] = off
+            off = _round_up(off + self.param_list[i].numel(), 4)
+        assert off == self.numel
+        with torch.no_grad():
+            for name in self.SECTIONS:
+                buf = getattr(self, name)
+                old = buf.clone()
+                buf.zero_()
+                for i, p in enumerate(self.param_list):
+                    k = p.numel()
+                    buf[new_off[i]:new_off[i] + k].copy_(old[self.offsets[i]:self.offsets[i] + k])
+            self.offsets = new_off
+            self.layout = layout
+            for i, p in enumerate(self.param_list):
+                p.data = self.view_of('params', i)
+        self.attach_grads()
+        self.sharded = {}
+        if self.optimizer is not None:
+            self.optimizer._make_state()
 
 
     # -- sharded optimizer state (see the module docstring) ---------------------

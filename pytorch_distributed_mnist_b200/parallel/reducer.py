@@ -58,6 +58,11 @@ def _d7(fn):
     fn.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
 
 
+@_lib.optional_decl('pdm_reducer_ready_order')
+def _d8(fn):
+    fn.argtypes = [c_void_p, c_void_p, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
+
+
 @_lib.optional_decl('pdm_reducer_destroy')
 def _d5(fn):
     fn.argtypes = [c_void_p]
@@ -112,6 +117,15 @@ class NativeReducer(object):
                                                   compute_stream, comm_stream, ctypes.byref(self._first),
                                                   ctypes.byref(self._count)), 'pdm_reducer_finalize')
         return self._first.value, self._count.value
+
+    def ready_order(self):
+        """``(order, held_back)``: parameter indices in the order they became ready in this pass, and whether
+        a completed bucket had to wait for an earlier one."""
+        out = (ctypes.c_int32 * self.n_params)()
+        n, held = ctypes.c_int32(0), ctypes.c_int32(0)
+        _lib.check(self._lib.pdm_reducer_ready_order(self._h, out, ctypes.byref(n), ctypes.byref(held)),
+                   'pdm_reducer_ready_order')
+        return list(out)[:n.value], bool(held.value)
 
     def state(self):
         nxt, launches, n_order = ctypes.c_int32(0), ctypes.c_int64(0), ctypes.c_int32(0)
