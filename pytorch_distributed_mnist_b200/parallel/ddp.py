@@ -276,9 +276,9 @@ class DistributedDataParallel(nn.Module):
             # rank 0 decides for everybody (the ranks may have seen different orders)
             if self._meta_store is not None:
                 if self.rank == 0:
-                    self._meta_store.set(self._tag + '/rebuild', ','.join(str(i) for i in decision).encode())
+                    self._meta_store.set(self._tag + '/rebuild', (','.join(str(i) for i in decision) or 'keep').encode())
                 raw = bytes(self._meta_store.get(self._tag + '/rebuild')).decode()
-                decision = [int(v) for v in raw.split(',')] if raw else []
+                decision = [int(v) for v in raw.split(',')] if raw != 'keep' else []
             else:
                 box = [decision]
                 dist.broadcast_object_list(box, src=0, group=self._process_group)
