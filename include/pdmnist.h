@@ -40,6 +40,10 @@ enum pdm_opt { PDM_OPT_ADAM = 0, PDM_OPT_SGD = 1, PDM_OPT_NONE = 2 };
 
 const char* pdm_last_error(void);
 int pdm_version(void);
+/* sizeof() of the structs below as this build sees them, for bindings to check their own declarations:
+ * 0 pdm_hyper, 1 pdm_peers, 2 pdm_net_step_args, 3 pdm_net_tc_args, 4 pdm_gemm_args, 5 pdm_cnn_params,
+ * 6 pdm_cnn_plan, 7 pdm_reducer_config; 0 for an unknown index. */
+size_t pdm_abi_sizeof(int which);
 /* 1 when the calling process can see a CUDA device of compute capability 10.x. */
 int pdm_device_ok(int device);
 

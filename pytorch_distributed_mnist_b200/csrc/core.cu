@@ -20,6 +20,22 @@ unsigned pdm_skew_ns(void) {
 
 extern "C" int pdm_version(void) { return 100; }
 
+// sizeof() of every struct that crosses the C ABI, so that a binding (ctypes, cffi, another compiler)
+// can check its own declaration against this build.  Order = order of appearance in pdmnist.h.
+extern "C" size_t pdm_abi_sizeof(int which) {
+  switch (which) {
+    case 0: return sizeof(pdm_hyper);
+    case 1: return sizeof(pdm_peers);
+    case 2: return sizeof(pdm_net_step_args);
+    case 3: return sizeof(pdm_net_tc_args);
+    case 4: return sizeof(pdm_gemm_args);
+    case 5: return sizeof(pdm_cnn_params);
+    case 6: return sizeof(pdm_cnn_plan);
+    case 7: return sizeof(pdm_reducer_config);
+    default: return 0;
+  }
+}
+
 extern "C" int pdm_device_ok(int device) {
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) {

@@ -55,3 +55,17 @@ def test_bucket_assignment_matches_python_twin(lib):
     got = assign_buckets(sizes)
     assert [sorted(b) for b in got] == [[4, 5, 6, 7], [0, 1, 2, 3]]
     assert sum(len(b) for b in assign_buckets(list(range(1, 200)), cap_bytes=1024)) == 199
+
+
+def test_ctypes_structs_match_the_header(lib):
+    """Every struct that crosses the C ABI has the size this build of the library compiled it with
+    (a field added to include/pdmnist.h but not to the ctypes mirror would silently shift everything after it)."""
+    from pytorch_distributed_mnist_b200.ops import cnn_engine, gemm
+    from pytorch_distributed_mnist_b200.parallel import reducer
+    lib.pdm_abi_sizeof.restype = ctypes.c_size_t
+    lib.pdm_abi_sizeof.argtypes = [ctypes.c_int]
+    mirrors = [_lib.Hyper, _lib.Peers, _lib.NetStepArgs, _lib.NetTcArgs, gemm.GemmArgs, cnn_engine.CnnParams,
+               cnn_engine.CnnPlan, reducer.ReducerConfig]
+    for which, cls in enumerate(mirrors):
+        assert lib.pdm_abi_sizeof(which) == ctypes.sizeof(cls), cls.__name__
+    assert lib.pdm_abi_sizeof(len(mirrors)) == 0
