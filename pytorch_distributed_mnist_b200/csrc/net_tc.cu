@@ -28,10 +28,12 @@
 //     (dlogits, already split) into every other CTA.
 //   * warp-specialised: 7 producer warps stream the NEXT step's rows (device memory, or pinned host
 //     memory over PCIe, optionally gathered through an index plan) while the current step computes;
-//     1 MMA-issuing warp; 4 epilogue/optimizer warps (TMEM lanes).
+//     1 MMA-issuing warp; 4 epilogue/optimizer warps (TMEM lanes).  Optimizer thread t of the 128
+//     owns column t % 64 and classes 5 (t / 64) .. +4: five weights with their moments in registers
+//     (threads 0-9 also keep a replica of the bias).
 //   * multi-GPU: the gradient of a CTA's columns is exchanged with the same CTA of every peer
-//     with the LL protocol of net_step.cu (8-byte {value, flag} units pushed over NVLink),
-//     summed in rank order (bit-identical replicas), inside the same kernel.
+//     with an LL protocol (16-byte {value, flag, value, flag} units pushed over NVLink by all 128
+//     epilogue threads), summed in rank order (bit-identical replicas), inside the same kernel.
 #include "common.cuh"
 
 #include <cuda_bf16.h>
