@@ -303,3 +303,44 @@ def test_native_reducer_launches_buckets_in_index_order():
         NativeReducer([0], [(0, 6)])
     with pytest.raises(RuntimeError, match='maps to bucket'):
         NativeReducer([1], [(0, 8)])
+
+
+def test_flat_state_relayout_moves_parameters_gradients_and_moments():
+    """FlatState.relayout (used by the reducer's bucket rebuild): values follow their parameter into the new
+    memory order, every view is re-created, training continues exactly as without the move."""
+    from pytorch_distributed_mnist_b200.parallel.flat import FlatState
+
+    def make():
+        torch.manual_seed(3)
+        return torch.nn.Sequential(torch.nn.Linear(7, 5), torch.nn.Linear(5, 3), torch.nn.Linear(3, 2))
+
+    a, b = make(), make()
+    oa = pdm.FusedAdam(a.parameters(), lr=1e-2)
+    ob = pdm.FusedAdam(b.parameters(), lr=1e-2)
+    x, y = torch.randn(6, 7), torch.randint(0, 2, (6,))
+
+    def step(m, o):
+        o.zero_grad()
+        torch.nn.functional.cross_entropy(m(x), y).backward()
+        o.step()
+
+    step(a, oa); step(b, ob)
+    flat = ob.flat
+    assert isinstance(flat, FlatState) and flat.layout == list(range(6))
+    flat.relayout([4, 5, 2, 3, 0, 1])                       # last layer first
+    assert flat.offsets[4] == 0 and flat.layout == [4, 5, 2, 3, 0, 1]
+    first = list(b.parameters())[4]
+    assert first.data_ptr() == flat.params.data_ptr() and first.grad.data_ptr() == flat.grads.data_ptr()
+    for p, q in zip(a.parameters(), b.parameters()):
+        assert torch.equal(p, q)
+    step(a, oa); step(b, ob)                                # Adam moments moved too, or this diverges
+    for p, q in zip(a.parameters(), b.parameters()):
+        torch.testing.assert_close(p, q, rtol=0, atol=0)
+    sa, sb = oa.state_dict()['state'], ob.state_dict()['state']
+    for k in sa:
+        assert torch.equal(sa[k]['exp_avg'], sb[k]['exp_avg']) and torch.equal(sa[k]['exp_avg_sq'], sb[k]['exp_avg_sq'])
+    with pytest.raises(ValueError):
+        flat.relayout([0, 1, 2])
+    flat.layout_frozen = True
+    with pytest.raises(RuntimeError, match='native engine'):
+        flat.relayout(list(range(6)))
